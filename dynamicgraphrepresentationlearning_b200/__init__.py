@@ -1,0 +1,15 @@
+"""B200-native WharfMH hot path: bulk random-walk generation and edge-batch walk maintenance.
+
+Public surface = the reference's (dygrl::WharfMH + namespace config), see wharfmh.py.  All compute is CUDA
+(sm_100a) behind the C ABI of include/wharfmh_b200.h; importing this package without the built library
+raises.
+"""
+from . import _capi
+from ._capi import (DEEPWALK, INIT_BURNIN, INIT_RANDOM, INIT_WEIGHT, NODE2VEC, NO_VERTEX, REF_SENTINEL, SEARCH_AUTO,
+                    SEARCH_INDEX, SEARCH_SCAN, WharfError)
+from .wharfmh import Config, WharfMH, szudzik_pair, szudzik_unpair
+
+_capi.load()   # fail loudly at import when the CUDA library is missing
+
+__all__ = ["Config", "WharfMH", "WharfError", "DEEPWALK", "NODE2VEC", "INIT_RANDOM", "INIT_BURNIN", "INIT_WEIGHT",
+           "SEARCH_AUTO", "SEARCH_INDEX", "SEARCH_SCAN", "NO_VERTEX", "REF_SENTINEL", "szudzik_pair", "szudzik_unpair"]

@@ -1,0 +1,165 @@
+// Shared device/host helpers of libwharfmh_b200 (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+namespace wharf
+{
+using u8  = uint8_t;
+using u32 = uint32_t;
+using u64 = uint64_t;
+using i64 = int64_t;
+
+constexpr u32 kNoVertex    = 0xFFFFFFFFu;   // "no vertex" in the walk matrix
+constexpr u32 kRefSentinel = 0xFFFFFFFEu;   // the reference's end-of-walk marker (graph/wharfmh.h:283,317)
+constexpr u32 kNoPos       = 0xFFFFFFFFu;   // "walk not affected" in the min-position array
+
+// Row descriptor of the device adjacency: neighbours of v live at pool[begin, begin + degree), ascending.
+// One aligned 8-byte load per walker step (never straddles a 32-byte sector).
+struct __align__(8) RowDesc
+{
+    u32 begin;
+    u32 degree;
+};
+
+struct CudaError : std::runtime_error
+{
+    cudaError_t code;
+    CudaError(cudaError_t c, const std::string& what) : std::runtime_error(what), code(c) {}
+};
+
+#define WHARF_CUDA(expr)                                                                              \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess)                                                                        \
+            throw ::wharf::CudaError(_e, std::string(#expr) + " failed: " + cudaGetErrorString(_e) +  \
+                                             " (" + __FILE__ + ":" + std::to_string(__LINE__) + ")"); \
+    } while (0)
+
+inline unsigned div_up(u64 a, u64 b) { return (unsigned) ((a + b - 1) / b); }
+
+// Grid for a grid-stride kernel: a whole number of waves on the 148-SM part, capped by the work.
+inline unsigned grid_for(u64 work_items, unsigned block, unsigned blocks_per_sm, int sm_count)
+{
+    u64 need = (work_items + block - 1) / block;
+    u64 full = (u64) sm_count * blocks_per_sm;
+    if (need == 0) need = 1;
+    return (unsigned) (need < full ? need : full);
+}
+
+// Owning device allocation (cudaMalloc).  Not copyable.
+template <class T>
+struct DeviceBuffer
+{
+    T*  ptr = nullptr;
+    u64 count = 0;
+
+    DeviceBuffer() = default;
+    DeviceBuffer(const DeviceBuffer&) = delete;
+    DeviceBuffer& operator=(const DeviceBuffer&) = delete;
+    DeviceBuffer(DeviceBuffer&& o) noexcept : ptr(o.ptr), count(o.count) { o.ptr = nullptr; o.count = 0; }
+    DeviceBuffer& operator=(DeviceBuffer&& o) noexcept
+    {
+        if (this != &o) { release(); ptr = o.ptr; count = o.count; o.ptr = nullptr; o.count = 0; }
+        return *this;
+    }
+    ~DeviceBuffer() { release(); }
+
+    void allocate(u64 n)
+    {
+        release();
+        if (n == 0) return;
+        cudaError_t e = cudaMalloc((void**) &ptr, n * sizeof(T));
+        if (e != cudaSuccess)
+        {
+            ptr = nullptr;
+            cudaGetLastError();
+            throw CudaError(e, "cudaMalloc of " + std::to_string(n * sizeof(T)) + " bytes failed: " + cudaGetErrorString(e));
+        }
+        count = n;
+    }
+    void ensure(u64 n) { if (n > count) allocate(n); }
+    void release()
+    {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        count = 0;
+    }
+    u64 bytes() const { return count * sizeof(T); }
+};
+
+#ifdef __CUDACC__
+// ---- integer helpers shared by kernels -------------------------------------------------------------
+
+// x % d for a 64-bit draw and a 32-bit degree (utility::Random::irand, utils/utility.h:220, whose int
+// argument is the degree).  Two chained 32-bit-divisor reductions: x = hi*2^32 + lo,
+// r1 = hi % d, result = (r1*2^32 + lo) % d; the second is done with one double-precision quotient
+// estimate (error <= 1) and an exact integer correction.
+__device__ __forceinline__ u32 mod_u64_u32(u64 x, u32 d)
+{
+    const u32 hi = (u32) (x >> 32);
+    const u32 r1 = hi % d;
+    const u64 t  = ((u64) r1 << 32) | (u32) x;                 // < d * 2^32
+    const double qd = __ddiv_rz(__ull2double_rz(t), (double) d);
+    u64 q = __double2ull_rz(qd);
+    i64 rem = (i64) (t - q * (u64) d);
+    if (rem < 0) rem += d;                                     // estimate one too high
+    if (rem >= (i64) d) rem -= d;                              // estimate one too low
+    return (u32) rem;
+}
+
+__device__ __forceinline__ u32 warp_sum(u32 v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide sum folded into one 64-bit atomic per block.
+__device__ __forceinline__ void block_add_u64(unsigned long long* target, u32 v)
+{
+    __shared__ u32 s_part[32];
+    v = warp_sum(v);
+    const u32 lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) s_part[wid] = v;
+    __syncthreads();
+    if (wid == 0)
+    {
+        u32 t = lane < ((blockDim.x + 31) >> 5) ? s_part[lane] : 0;
+        t = warp_sum(t);
+        if (lane == 0 && t) atomicAdd(target, (unsigned long long) t);
+    }
+    __syncthreads();
+}
+
+// lower_bound over an ascending u32 array slice.
+__device__ __forceinline__ u32 lower_bound_u32(const u32* __restrict__ a, u32 n, u32 key)
+{
+    u32 lo = 0, hi = n;
+    while (lo < hi)
+    {
+        u32 mid = (lo + hi) >> 1;
+        if (__ldg(a + mid) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// Largest i with a[i] <= key in an ascending u64 array of n >= 1 entries whose a[0] <= key.
+__device__ __forceinline__ u32 upper_segment_u64(const u64* __restrict__ a, u32 n, u64 key)
+{
+    u32 lo = 0, hi = n;
+    while (hi - lo > 1)
+    {
+        u32 mid = (lo + hi) >> 1;
+        if (__ldg(a + mid) <= key) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+#endif  // __CUDACC__
+
+}  // namespace wharf

@@ -1,0 +1,997 @@
+// Host-side engine and the C ABI of include/wharfmh_b200.h.
+//
+// Mirrors dygrl::WharfMH (graph/wharfmh.h:21): graph construction, generate_initial_random_walks (:250),
+// insert/delete_edges_batch (:439/:588) with batch_walk_update (:733), walk retrieval (:365,:404),
+// flatten_graph (:175), destroy/destroy_index (:228,:237), memory_footprint (:928) and the four timers of
+// config/config.h:10-14.  All compute runs in the CUDA kernels of this directory; there is no host fallback.
+#include "engine.hpp"
+#include "pairings.cuh"
+#include "rng.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <string>
+
+using namespace wharf;
+
+namespace
+{
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg)
+{
+    g_last_error = msg;
+    return code;
+}
+
+template <class F>
+int guarded(F&& f)
+{
+    try
+    {
+        return f();
+    }
+    catch (const CudaError& e)
+    {
+        cudaGetLastError();
+        return fail(e.code == cudaErrorMemoryAllocation ? WMH_ERR_OOM : WMH_ERR_CUDA, e.what());
+    }
+    catch (const std::bad_alloc&)
+    {
+        return fail(WMH_ERR_OOM, "host allocation failed");
+    }
+    catch (const std::exception& e)
+    {
+        return fail(WMH_ERR_INVALID, e.what());
+    }
+}
+}  // namespace
+
+struct wmh_engine
+{
+    wmh_config cfg{};
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    u64 launches = 0, library_calls = 0;
+
+    DeviceGraph g;
+    DeviceBuffer<u64> draw;            // X[wpv][L]
+    u32 draw_wpv = 0, draw_len = 0;
+
+    DeviceBuffer<u32> walks;           // [L][w_local]
+    bool have_walks = false;
+    u64 w_local = 0;
+    u32 n_local = 0;
+    u32 walks_L = 0, walks_wpv = 0;
+
+    DeviceIndex index;
+    DeviceBuffer<u64> codes;           // paired corpus (compressed_walks.h), valid while index.valid && codes_valid
+    bool codes_valid = false;
+
+    DeviceBuffer<u32> bitmap;          // touched vertices of the current batch
+    DeviceBuffer<u32> min_pos;         // w_local
+    DeviceBuffer<u32> aff_ids, aff_pos;
+    u64 n_affected = 0;
+    DeviceBuffer<u32> touched;         // distinct sources of the last batch
+    u64 n_touched = 0;
+
+    DeviceBuffer<unsigned long long> d_steps;
+    u64 last_steps = 0;
+    double timers[5] = {0, 0, 0, 0, 0};
+    double last_walk_kernel_ms = 0;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    DeviceBuffer<u32> small;           // misc tiny results
+
+    LaunchCtx lc() { return LaunchCtx{stream, sm_count, &launches, &library_calls}; }
+    void bind() const { WHARF_CUDA(cudaSetDevice(cfg.device)); }
+
+    ~wmh_engine()
+    {
+        cudaSetDevice(cfg.device);
+        if (stream) cudaStreamSynchronize(stream);
+        for (auto& e : ev) if (e) cudaEventDestroy(e);
+        // buffers release in their destructors; the stream goes last
+    }
+};
+
+namespace
+{
+void validate_config(const wmh_config& c)
+{
+    if (c.walks_per_vertex == 0 || c.walks_per_vertex > 255) throw std::invalid_argument("walks_per_vertex must be in 1..255 (uint8_t in the reference)");
+    if (c.walk_length == 0 || c.walk_length > 255) throw std::invalid_argument("walk_length must be in 1..255 (uint8_t in the reference)");
+    if (c.model > WMH_NODE2VEC) throw std::invalid_argument("unrecognized random walking model");          // wharfmh.h:269-271
+    if (c.init_strategy > WMH_INIT_WEIGHT) throw std::invalid_argument("unrecognized sampler init strategy");
+    if (c.search_mode > WMH_SEARCH_SCAN) throw std::invalid_argument("unrecognized search mode");
+    if (c.world == 0 || c.rank >= c.world) throw std::invalid_argument("rank must be < world, world >= 1");
+    if (c.model == WMH_NODE2VEC && !c.deterministic && (!(c.param_p > 0) || !(c.param_q > 0))) throw std::invalid_argument("node2vec p and q must be positive");
+}
+
+std::unique_ptr<wmh_engine> make_engine(const wmh_config* cfg)
+{
+    if (!cfg) throw std::invalid_argument("null config");
+    validate_config(*cfg);
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+    {
+        cudaGetLastError();
+        throw CudaError(e == cudaSuccess ? cudaErrorNoDevice : e, "no CUDA device available: libwharfmh_b200 has no CPU path");
+    }
+    if (cfg->device < 0 || cfg->device >= count) throw std::invalid_argument("device ordinal out of range");
+    auto eng = std::make_unique<wmh_engine>();
+    eng->cfg = *cfg;
+    eng->bind();
+    cudaDeviceProp prop{};
+    WHARF_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major < 10) throw CudaError(cudaErrorInvalidDevice, std::string("device '") + prop.name + "' is not sm_100-class; this library carries sm_100a code only");
+    eng->sm_count = prop.multiProcessorCount;
+    WHARF_CUDA(cudaStreamCreateWithFlags(&eng->stream, cudaStreamNonBlocking));
+    for (auto& ev : eng->ev) WHARF_CUDA(cudaEventCreate(&ev));
+    // keep stream-ordered scratch in the pool between batches
+    cudaMemPool_t pool;
+    WHARF_CUDA(cudaDeviceGetDefaultMemPool(&pool, cfg->device));
+    unsigned long long threshold = ~0ull;
+    WHARF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+    eng->d_steps.allocate(1);
+    eng->small.allocate(16);
+    return eng;
+}
+
+void finish_graph(wmh_engine& e, u64 n, u64 m, const u64* d_offsets, const u32* d_edges)
+{
+    if (n == 0) throw std::invalid_argument("graph needs at least one vertex");
+    if (n >= 0xFFFFFFFEull) throw std::invalid_argument("vertex ids must fit 32 bits");
+    if (m >= (1ull << 32)) throw std::invalid_argument("more than 2^32 directed edges are not supported by the u32 row descriptors");
+    auto lc = e.lc();
+    e.g.n = n;
+    e.g.m = m;
+    e.g.desc.allocate(n);
+    u64 capacity = m + m / 2 + (1u << 20);
+    if (capacity >= (1ull << 32)) capacity = (1ull << 32) - 1;
+    e.g.pool.allocate(capacity);
+    e.g.version.allocate(n);
+    WHARF_CUDA(cudaMemsetAsync(e.g.version.ptr, 0, n * sizeof(u32), e.stream));
+    if (m) WHARF_CUDA(cudaMemcpyAsync(e.g.pool.ptr, d_edges, m * sizeof(u32), cudaMemcpyDeviceToDevice, e.stream));
+    if (d_offsets) graph_build_desc(lc, d_offsets, n, m, e.g.desc.ptr);
+    else WHARF_CUDA(cudaMemsetAsync(e.g.desc.ptr, 0, n * sizeof(RowDesc), e.stream));
+    e.g.pool_used = m;
+    e.bitmap.allocate((n + 31) / 32);
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+}
+
+u32 local_starts(u64 n, u32 rank, u32 world) { return rank < n ? (u32) ((n - rank + world - 1) / world) : 0; }
+
+WalkParams walk_params(wmh_engine& e)
+{
+    WalkParams wp;
+    wp.desc = e.g.desc.ptr;
+    wp.pool = e.g.pool.ptr;
+    wp.version = e.g.version.ptr;
+    wp.memo = e.g.memo.ptr;
+    wp.draw = e.draw.ptr;
+    wp.walks = e.walks.ptr;
+    wp.n = e.g.n;
+    wp.w_local = e.w_local;
+    wp.n_local = e.n_local;
+    wp.wpv = e.walks_wpv;
+    wp.L = e.walks_L;
+    wp.rank = e.cfg.rank;
+    wp.world = e.cfg.world;
+    wp.model = e.cfg.model;
+    wp.deterministic = e.cfg.deterministic;
+    wp.init_strategy = e.cfg.init_strategy;
+    wp.p = e.cfg.param_p;
+    wp.q = e.cfg.param_q;
+    wp.seed = e.cfg.seed;
+    return wp;
+}
+
+bool needs_memo(const wmh_engine& e) { return !e.cfg.deterministic && e.cfg.model == WMH_NODE2VEC; }
+
+void ensure_memo(wmh_engine& e)
+{
+    if (!needs_memo(e)) return;
+    if (e.g.memo.count != e.g.pool.count)
+    {
+        e.g.memo.allocate(e.g.pool.count);
+        WHARF_CUDA(cudaMemsetAsync(e.g.memo.ptr, 0xFF, e.g.memo.bytes(), e.stream));
+    }
+}
+
+void generate(wmh_engine& e)
+{
+    e.bind();
+    validate_config(e.cfg);
+    auto lc = e.lc();
+    const u32 wpv = e.cfg.walks_per_vertex, L = e.cfg.walk_length;
+    e.n_local = local_starts(e.g.n, e.cfg.rank, e.cfg.world);
+    e.w_local = (u64) e.n_local * wpv;
+    if (e.w_local >= (1ull << 32)) throw std::invalid_argument("more than 2^32 walks per rank are not supported");
+    e.walks_L = L;
+    e.walks_wpv = wpv;
+    e.have_walks = false;
+    e.index.valid = false;
+    e.codes_valid = false;
+    e.n_affected = 0;
+    e.walks.ensure(std::max<u64>(1, e.w_local * L));
+    e.min_pos.ensure(std::max<u64>(1, e.w_local));
+    if (e.draw_wpv != wpv || e.draw_len != L)
+    {
+        const std::vector<u64> table = make_draw_table(wpv, L);
+        e.draw.allocate(table.size());
+        WHARF_CUDA(cudaMemcpyAsync(e.draw.ptr, table.data(), table.size() * sizeof(u64), cudaMemcpyHostToDevice, e.stream));
+        WHARF_CUDA(cudaStreamSynchronize(e.stream));
+        e.draw_wpv = wpv;
+        e.draw_len = L;
+    }
+    if (needs_memo(e))
+    {
+        e.g.memo.release();          // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90)
+        ensure_memo(e);
+    }
+    WHARF_CUDA(cudaMemsetAsync(e.d_steps.ptr, 0, 8, e.stream));
+    WHARF_CUDA(cudaEventRecord(e.ev[0], e.stream));
+    walks_generate(lc, walk_params(e), e.d_steps.ptr);
+    WHARF_CUDA(cudaEventRecord(e.ev[1], e.stream));
+    unsigned long long steps = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&steps, e.d_steps.ptr, 8, cudaMemcpyDeviceToHost, e.stream));
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    float ms = 0;
+    WHARF_CUDA(cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]));
+    e.last_walk_kernel_ms = ms;
+    e.timers[WMH_TIMER_GENERATE] = ms * 1e-3;
+    e.last_steps = steps;
+    e.have_walks = true;
+    if (e.cfg.search_mode == WMH_SEARCH_INDEX) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+}
+
+// Shared body of insert_edges_batch / delete_edges_batch (wharfmh.h:439-576 / 588-726).
+void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, bool is_delete, bool remove_dups, bool apply_walk_updates)
+{
+    auto lc = e.lc();
+    e.n_affected = 0;
+    e.n_touched = 0;
+    e.last_steps = 0;
+    e.last_walk_kernel_ms = 0;
+    if (count == 0) return;
+
+    WHARF_CUDA(cudaMemsetAsync(e.small.ptr, 0, 4, e.stream));
+    graph_check_ids(lc, d_pairs, count, e.g.n, e.small.ptr);
+    u32 bad = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&bad, e.small.ptr, 4, cudaMemcpyDeviceToHost, e.stream));
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    if (bad) throw std::invalid_argument("edge batch names a vertex id >= number_of_vertices()");   // would change walk_id % n (wharfmh.h:254,368)
+
+    // ---- graph update (graph_update_time_on_{insert,delete}, wharfmh.h:542-544 / 692-694) ----
+    WHARF_CUDA(cudaEventRecord(e.ev[0], e.stream));
+    PreparedBatch batch;
+    graph_prepare_batch(lc, d_pairs, count, remove_dups, e.g.n, batch, d_sorted_out);
+    WHARF_CUDA(cudaMemsetAsync(e.bitmap.ptr, 0, e.bitmap.bytes(), e.stream));
+    if (needs_memo(e) && e.have_walks) ensure_memo(e);
+    graph_apply_batch(lc, e.g, batch, is_delete, e.bitmap.ptr);
+    e.codes_valid = false;
+    e.n_touched = batch.n_sources;
+    if (batch.n_sources)
+    {
+        e.touched.ensure(batch.n_sources);
+        WHARF_CUDA(cudaMemcpyAsync(e.touched.ptr, batch.sources.ptr, batch.n_sources * sizeof(u32), cudaMemcpyDeviceToDevice, e.stream));
+    }
+    WHARF_CUDA(cudaEventRecord(e.ev[1], e.stream));
+
+    // ---- walk update (walk_update_time_on_{insert,delete}, wharfmh.h:546-549 / 696-699) ----
+    float walk_kernel_ms = 0;
+    if (e.have_walks && batch.n_sources && e.w_local)
+    {
+        // 1. map of changes: earliest position of every walk on a touched vertex (wharfmh.h:519-537)
+        bool use_index = false;
+        if (e.cfg.search_mode == WMH_SEARCH_INDEX)
+        {
+            if (!e.index.valid) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+            use_index = true;
+        }
+        else if (e.cfg.search_mode == WMH_SEARCH_AUTO && e.index.valid)
+        {
+            const u64 visited = index_count_touched(lc, e.index, batch.sources.ptr, batch.n_sources);
+            use_index = visited * 8 < e.w_local * e.walks_L;    // a random index entry costs about 8 streamed cells
+        }
+        if (use_index)
+        {
+            fill_u32(lc, e.min_pos.ptr, e.w_local, kNoPos);
+            index_search(lc, e.index, batch.sources.ptr, batch.n_sources, e.w_local, e.min_pos.ptr);
+        }
+        else
+        {
+            walks_scan_touched(lc, e.walks.ptr, e.w_local, e.walks_L, e.bitmap.ptr, e.min_pos.ptr);
+        }
+        e.aff_ids.ensure(e.w_local);
+        e.aff_pos.ensure(e.w_local);
+        e.n_affected = walks_compact_affected(lc, e.min_pos.ptr, e.w_local, e.aff_ids.ptr, e.aff_pos.ptr);
+
+        // 2. re-walk every affected walk from its earliest affected position (wharfmh.h:761-859)
+        if (apply_walk_updates && e.n_affected)
+        {
+            WHARF_CUDA(cudaMemsetAsync(e.d_steps.ptr, 0, 8, e.stream));
+            WHARF_CUDA(cudaEventRecord(e.ev[3], e.stream));
+            walks_rewalk(lc, walk_params(e), e.aff_ids.ptr, e.aff_pos.ptr, e.n_affected, e.d_steps.ptr);
+            WHARF_CUDA(cudaEventRecord(e.ev[4], e.stream));
+            unsigned long long steps = 0;
+            WHARF_CUDA(cudaMemcpyAsync(&steps, e.d_steps.ptr, 8, cudaMemcpyDeviceToHost, e.stream));
+            WHARF_CUDA(cudaStreamSynchronize(e.stream));
+            e.last_steps = steps;
+            WHARF_CUDA(cudaEventElapsedTime(&walk_kernel_ms, e.ev[3], e.ev[4]));
+            // 3. index maintenance (wharfmh.h:861-922): the sorted index is re-derived from the patched corpus
+            e.index.valid = false;
+            if (e.cfg.search_mode == WMH_SEARCH_INDEX) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+        }
+    }
+    WHARF_CUDA(cudaEventRecord(e.ev[2], e.stream));
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    float graph_ms = 0, walk_ms = 0;
+    WHARF_CUDA(cudaEventElapsedTime(&graph_ms, e.ev[0], e.ev[1]));
+    WHARF_CUDA(cudaEventElapsedTime(&walk_ms, e.ev[1], e.ev[2]));
+    e.timers[is_delete ? WMH_TIMER_GRAPH_UPDATE_DELETE : WMH_TIMER_GRAPH_UPDATE_INSERT] += graph_ms * 1e-3;
+    e.timers[is_delete ? WMH_TIMER_WALK_UPDATE_DELETE : WMH_TIMER_WALK_UPDATE_INSERT] += walk_ms * 1e-3;
+    e.last_walk_kernel_ms = walk_kernel_ms;
+}
+
+int update_host(wmh_engine* e, u64 m, u32* edges, int sorted, int remove_dups, int apply, u64* n_affected, bool is_delete)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (m && !edges) return fail(WMH_ERR_INVALID, "null edge batch");
+    return guarded([&] {
+        e->bind();
+        Scratch<u32> d_pairs(e->stream, 2 * m), d_sorted;
+        if (m) WHARF_CUDA(cudaMemcpyAsync(d_pairs.ptr, edges, 2 * m * sizeof(u32), cudaMemcpyHostToDevice, e->stream));
+        if (!sorted && m) d_sorted.allocate(e->stream, 2 * m);
+        update(*e, m, d_pairs.ptr, d_sorted.ptr, is_delete, remove_dups != 0, apply != 0);
+        if (!sorted && m)
+        {
+            // the reference sorts the caller's array in place (wharfmh.h:452 -> :1056)
+            WHARF_CUDA(cudaMemcpyAsync(edges, d_sorted.ptr, 2 * m * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+            WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        }
+        if (n_affected) *n_affected = e->n_affected;
+        return (int) WMH_OK;
+    });
+}
+
+int update_device(wmh_engine* e, u64 m, const u32* d_edges, int remove_dups, int apply, u64* n_affected, bool is_delete)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (m && !d_edges) return fail(WMH_ERR_INVALID, "null edge batch");
+    return guarded([&] {
+        e->bind();
+        update(*e, m, d_edges, nullptr, is_delete, remove_dups != 0, apply != 0);
+        if (n_affected) *n_affected = e->n_affected;
+        return (int) WMH_OK;
+    });
+}
+
+i64 global_to_local(const wmh_engine& e, u64 walk_id)
+{
+    const u64 n = e.g.n;
+    if (!e.have_walks || walk_id >= n * e.walks_wpv) return -1;
+    const u64 replica = walk_id / n, start = walk_id % n;
+    if (start % e.cfg.world != e.cfg.rank) return -1;
+    return (i64) (replica * e.n_local + start / e.cfg.world);
+}
+
+u64 local_to_global(const wmh_engine& e, u64 local)
+{
+    const u64 replica = local / e.n_local, s = local % e.n_local;
+    return replica * e.g.n + s * e.cfg.world + e.cfg.rank;
+}
+
+void fetch_walk(wmh_engine& e, u64 local, std::vector<u32>& row)
+{
+    auto lc = e.lc();
+    const u32 L = e.walks_L;
+    Scratch<u32> d_id(e.stream, 1), d_row(e.stream, L);
+    const u32 id = (u32) local;
+    WHARF_CUDA(cudaMemcpyAsync(d_id.ptr, &id, 4, cudaMemcpyHostToDevice, e.stream));
+    walks_gather_rows(lc, e.walks.ptr, e.w_local, L, d_id.ptr, 1, d_row.ptr);
+    row.resize(L);
+    WHARF_CUDA(cudaMemcpyAsync(row.data(), d_row.ptr, L * sizeof(u32), cudaMemcpyDeviceToHost, e.stream));
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+}
+
+void ensure_index(wmh_engine& e)
+{
+    if (!e.have_walks) throw std::logic_error("walks have not been generated");
+    if (!e.index.valid)
+    {
+        auto lc = e.lc();
+        index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+        e.codes_valid = false;
+    }
+}
+
+void ensure_codes(wmh_engine& e)
+{
+    ensure_index(e);
+    if (e.codes_valid) return;
+    if (e.g.n * e.walks_wpv * (u64) e.walks_L >= (1ull << 32)) throw std::domain_error("paired corpus needs walks * walk_length < 2^32 (u64 Szudzik domain)");
+    auto lc = e.lc();
+    e.codes.ensure(std::max<u64>(1, e.index.entries));
+    compressed_walks_encode(lc, e.index, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.n_local, e.cfg.rank, e.cfg.world, e.codes.ptr);
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    e.codes_valid = true;
+}
+
+struct DefaultCtx
+{
+    u64 launches = 0, lib = 0;
+    LaunchCtx lc;
+    explicit DefaultCtx(int device)
+    {
+        int count = 0;
+        if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count)
+        {
+            cudaGetLastError();
+            throw CudaError(cudaErrorNoDevice, "no usable CUDA device: libwharfmh_b200 has no CPU path");
+        }
+        WHARF_CUDA(cudaSetDevice(device));
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        lc = LaunchCtx{nullptr, sms, &launches, &lib};
+    }
+};
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+extern "C" {
+
+void wmh_default_config(wmh_config* cfg)
+{
+    if (!cfg) return;
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->walks_per_vertex = 10;            // config/globals.h:7
+    cfg->walk_length = 80;                 // config/globals.h:10
+    cfg->model = WMH_NODE2VEC;             // config/globals.h:14
+    cfg->param_p = 4.0f;                   // config/globals.h:17
+    cfg->param_q = 1.0f;                   // config/globals.h:20
+    cfg->init_strategy = WMH_INIT_WEIGHT;  // config/globals.h:23
+    cfg->deterministic = 1;                // config/globals.h:29
+    cfg->search_mode = WMH_SEARCH_AUTO;
+    cfg->seed = 0;
+    cfg->device = 0;
+    cfg->rank = 0;
+    cfg->world = 1;
+}
+
+const char* wmh_last_error(void) { return g_last_error.c_str(); }
+const char* wmh_version(void) { return "wharfmh_b200 0.1 (sm_100a)"; }
+
+int wmh_create(wmh_engine** out, uint64_t n, uint64_t m, const uint64_t* offsets, const uint32_t* edges, const wmh_config* cfg)
+{
+    if (!out) return fail(WMH_ERR_INVALID, "null out");
+    *out = nullptr;
+    if (!offsets || (m && !edges)) return fail(WMH_ERR_INVALID, "null CSR arrays");
+    return guarded([&] {
+        auto e = make_engine(cfg);
+        Scratch<u64> d_off(e->stream, n);
+        Scratch<u32> d_edges(e->stream, m);
+        WHARF_CUDA(cudaMemcpyAsync(d_off.ptr, offsets, n * sizeof(u64), cudaMemcpyHostToDevice, e->stream));
+        if (m) WHARF_CUDA(cudaMemcpyAsync(d_edges.ptr, edges, m * sizeof(u32), cudaMemcpyHostToDevice, e->stream));
+        finish_graph(*e, n, m, d_off.ptr, d_edges.ptr);
+        *out = e.release();
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_create_device(wmh_engine** out, uint64_t n, uint64_t m, const uint64_t* d_offsets, const uint32_t* d_edges, const wmh_config* cfg)
+{
+    if (!out) return fail(WMH_ERR_INVALID, "null out");
+    *out = nullptr;
+    if (!d_offsets || (m && !d_edges)) return fail(WMH_ERR_INVALID, "null CSR arrays");
+    return guarded([&] {
+        auto e = make_engine(cfg);
+        WHARF_CUDA(cudaDeviceSynchronize());     // the caller's producer streams are unknown to us
+        finish_graph(*e, n, m, d_offsets, d_edges);
+        *out = e.release();
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_create_empty(wmh_engine** out, uint64_t n, const wmh_config* cfg)
+{
+    if (!out) return fail(WMH_ERR_INVALID, "null out");
+    *out = nullptr;
+    return guarded([&] {
+        auto e = make_engine(cfg);
+        finish_graph(*e, n, 0, nullptr, nullptr);
+        *out = e.release();
+        return (int) WMH_OK;
+    });
+}
+
+void wmh_destroy(wmh_engine* e)
+{
+    if (!e) return;
+    cudaStream_t s = e->stream;
+    int device = e->cfg.device;
+    delete e;
+    cudaSetDevice(device);
+    if (s) cudaStreamDestroy(s);
+}
+
+int wmh_destroy_index(wmh_engine* e)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    return guarded([&] {
+        e->bind();
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        e->have_walks = false;
+        e->index.valid = false;
+        e->index.cells.release();
+        e->index.ptr.release();
+        e->codes.release();
+        e->codes_valid = false;
+        e->walks.release();
+        e->min_pos.release();
+        e->aff_ids.release();
+        e->aff_pos.release();
+        e->n_affected = 0;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_set_config(wmh_engine* e, const wmh_config* cfg)
+{
+    if (!e || !cfg) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        validate_config(*cfg);
+        if (cfg->device != e->cfg.device || cfg->rank != e->cfg.rank || cfg->world != e->cfg.world)
+            throw std::invalid_argument("device, rank and world are fixed at creation");
+        if (e->have_walks && (cfg->walks_per_vertex != e->walks_wpv || cfg->walk_length != e->walks_L))
+            throw std::logic_error("walks_per_vertex / walk_length cannot change while a corpus exists: call wmh_destroy_index first");
+        e->cfg = *cfg;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_get_config(const wmh_engine* e, wmh_config* cfg)
+{
+    if (!e || !cfg) return fail(WMH_ERR_INVALID, "null argument");
+    *cfg = e->cfg;
+    return WMH_OK;
+}
+
+uint64_t wmh_number_of_vertices(const wmh_engine* e) { return e ? e->g.n : 0; }
+uint64_t wmh_number_of_edges(const wmh_engine* e) { return e ? e->g.m : 0; }
+
+int wmh_flatten_graph(wmh_engine* e, uint64_t* row_ptr, uint32_t* col)
+{
+    if (!e || !row_ptr) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        e->bind();
+        auto lc = e->lc();
+        Scratch<u64> d_ptr(e->stream, e->g.n + 1);
+        Scratch<u32> d_col(e->stream, col ? e->g.m : 0);
+        graph_flatten(lc, e->g, d_ptr.ptr, col ? d_col.ptr : nullptr);
+        WHARF_CUDA(cudaMemcpyAsync(row_ptr, d_ptr.ptr, (e->g.n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+        if (col && e->g.m) WHARF_CUDA(cudaMemcpyAsync(col, d_col.ptr, e->g.m * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_degree(wmh_engine* e, uint32_t vertex, uint64_t* degree)
+{
+    if (!e || !degree) return fail(WMH_ERR_INVALID, "null argument");
+    if (vertex >= e->g.n) return fail(WMH_ERR_RANGE, "vertex out of range");
+    return guarded([&] {
+        e->bind();
+        RowDesc d;
+        WHARF_CUDA(cudaMemcpyAsync(&d, e->g.desc.ptr + vertex, sizeof(d), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        *degree = d.degree;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_neighbors(wmh_engine* e, uint32_t vertex, uint32_t* out, uint64_t capacity, uint64_t* degree)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null argument");
+    if (vertex >= e->g.n) return fail(WMH_ERR_RANGE, "vertex out of range");
+    return guarded([&] {
+        e->bind();
+        RowDesc d;
+        WHARF_CUDA(cudaMemcpyAsync(&d, e->g.desc.ptr + vertex, sizeof(d), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        if (degree) *degree = d.degree;
+        if (out)
+        {
+            if (capacity < d.degree) return fail(WMH_ERR_RANGE, "neighbour buffer too small");
+            if (d.degree) WHARF_CUDA(cudaMemcpyAsync(out, e->g.pool.ptr + d.begin, d.degree * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+            WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        }
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_generate_initial_random_walks(wmh_engine* e)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    return guarded([&] {
+        generate(*e);
+        return (int) WMH_OK;
+    });
+}
+
+uint64_t wmh_last_steps(const wmh_engine* e) { return e ? e->last_steps : 0; }
+uint64_t wmh_number_of_walks(const wmh_engine* e) { return e ? e->g.n * (e->have_walks ? e->walks_wpv : e->cfg.walks_per_vertex) : 0; }
+uint64_t wmh_number_of_local_walks(const wmh_engine* e)
+{
+    if (!e) return 0;
+    return e->have_walks ? e->w_local : (u64) local_starts(e->g.n, e->cfg.rank, e->cfg.world) * e->cfg.walks_per_vertex;
+}
+
+int wmh_insert_edges_batch(wmh_engine* e, uint64_t m, uint32_t* edges, int sorted, int remove_dups, uint64_t, int apply, uint64_t* n_affected)
+{ return update_host(e, m, edges, sorted, remove_dups, apply, n_affected, false); }
+int wmh_delete_edges_batch(wmh_engine* e, uint64_t m, uint32_t* edges, int sorted, int remove_dups, uint64_t, int apply, uint64_t* n_affected)
+{ return update_host(e, m, edges, sorted, remove_dups, apply, n_affected, true); }
+int wmh_insert_edges_batch_device(wmh_engine* e, uint64_t m, const uint32_t* d_edges, int remove_dups, int apply, uint64_t* n_affected)
+{ return update_device(e, m, d_edges, remove_dups, apply, n_affected, false); }
+int wmh_delete_edges_batch_device(wmh_engine* e, uint64_t m, const uint32_t* d_edges, int remove_dups, int apply, uint64_t* n_affected)
+{ return update_device(e, m, d_edges, remove_dups, apply, n_affected, true); }
+
+int wmh_affected_walks(wmh_engine* e, uint64_t* ids, uint32_t* positions, uint64_t capacity)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (capacity < e->n_affected) return fail(WMH_ERR_RANGE, "affected-walk buffer too small");
+    return guarded([&] {
+        e->bind();
+        const u64 k = e->n_affected;
+        if (k == 0) return (int) WMH_OK;
+        std::vector<u32> local(k);
+        WHARF_CUDA(cudaMemcpyAsync(local.data(), e->aff_ids.ptr, k * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+        if (positions) WHARF_CUDA(cudaMemcpyAsync(positions, e->aff_pos.ptr, k * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        if (ids) for (u64 i = 0; i < k; i++) ids[i] = local_to_global(*e, local[i]);
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_affected_walks_device(wmh_engine* e, const uint32_t** d_local_ids, const uint32_t** d_positions, uint64_t* count)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (d_local_ids) *d_local_ids = e->aff_ids.ptr;
+    if (d_positions) *d_positions = e->aff_pos.ptr;
+    if (count) *count = e->n_affected;
+    return WMH_OK;
+}
+
+int wmh_touched_vertices(wmh_engine* e, uint32_t* out, uint64_t capacity, uint64_t* count)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (count) *count = e->n_touched;
+    if (!out) return WMH_OK;
+    if (capacity < e->n_touched) return fail(WMH_ERR_RANGE, "touched-vertex buffer too small");
+    return guarded([&] {
+        e->bind();
+        if (e->n_touched) WHARF_CUDA(cudaMemcpyAsync(out, e->touched.ptr, e->n_touched * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_walk(wmh_engine* e, uint64_t walk_id, uint32_t* vertices, uint32_t* length)
+{
+    if (!e || !vertices) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    const i64 local = global_to_local(*e, walk_id);
+    if (local < 0) return fail(WMH_ERR_RANGE, "walk id not owned by this rank");
+    return guarded([&] {
+        e->bind();
+        std::vector<u32> row;
+        fetch_walk(*e, (u64) local, row);
+        u32 len = 0;
+        while (len < e->walks_L && row[len] != kNoVertex) len++;
+        std::memcpy(vertices, row.data(), e->walks_L * sizeof(u32));
+        if (length) *length = len;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_walk_string(wmh_engine* e, uint64_t walk_id, char* buf, size_t capacity, size_t* needed)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    const i64 local = global_to_local(*e, walk_id);
+    if (local < 0) return fail(WMH_ERR_RANGE, "walk id not owned by this rank");
+    return guarded([&] {
+        e->bind();
+        std::vector<u32> row;
+        fetch_walk(*e, (u64) local, row);
+        std::string s;
+        for (u32 p = 0; p < e->walks_L && row[p] != kNoVertex; p++) { s += std::to_string(row[p]); s += ' '; }   // wharfmh.h:376
+        if (needed) *needed = s.size() + 1;
+        if (buf)
+        {
+            if (capacity < s.size() + 1) return fail(WMH_ERR_RANGE, "string buffer too small");
+            std::memcpy(buf, s.c_str(), s.size() + 1);
+        }
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_vertex_at_walk(wmh_engine* e, uint64_t walk_id, uint32_t position, uint32_t* vertex)
+{
+    if (!e || !vertex) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    if (position >= e->walks_L) return fail(WMH_ERR_RANGE, "position out of range");
+    const i64 local = global_to_local(*e, walk_id);
+    if (local < 0) return fail(WMH_ERR_RANGE, "walk id not owned by this rank");
+    return guarded([&] {
+        e->bind();
+        WHARF_CUDA(cudaMemcpyAsync(vertex, e->walks.ptr + (u64) position * e->w_local + (u64) local, 4, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_walks_copy(wmh_engine* e, uint64_t first, uint64_t count, uint32_t* out)
+{
+    if (!e || (count && !out)) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    if (first + count > e->w_local) return fail(WMH_ERR_RANGE, "walk range out of bounds");
+    return guarded([&] {
+        e->bind();
+        auto lc = e->lc();
+        const u32 L = e->walks_L;
+        const u64 chunk = std::max<u64>(1, (64ull << 20) / L);              // 256 MiB staging
+        Scratch<u32> stage(e->stream, std::min(chunk, std::max<u64>(count, 1)) * L);
+        for (u64 done = 0; done < count; done += chunk)
+        {
+            const u64 c = std::min(chunk, count - done);
+            walks_transpose_rows(lc, e->walks.ptr, e->w_local, L, first + done, c, stage.ptr);
+            WHARF_CUDA(cudaMemcpyAsync(out + done * L, stage.ptr, c * L * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+            WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        }
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_walks_gather(wmh_engine* e, const uint32_t* local_ids, uint64_t count, uint32_t* out)
+{
+    if (!e || (count && (!out || !local_ids))) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    for (u64 i = 0; i < count; i++) if (local_ids[i] >= e->w_local) return fail(WMH_ERR_RANGE, "local walk id out of range");
+    return guarded([&] {
+        e->bind();
+        auto lc = e->lc();
+        const u32 L = e->walks_L;
+        Scratch<u32> d_ids(e->stream, count), d_rows(e->stream, count * L);
+        if (count == 0) return (int) WMH_OK;
+        WHARF_CUDA(cudaMemcpyAsync(d_ids.ptr, local_ids, count * sizeof(u32), cudaMemcpyHostToDevice, e->stream));
+        walks_gather_rows(lc, e->walks.ptr, e->w_local, L, d_ids.ptr, count, d_rows.ptr);
+        WHARF_CUDA(cudaMemcpyAsync(out, d_rows.ptr, count * L * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
+uint64_t wmh_local_to_global_walk(const wmh_engine* e, uint64_t local_walk)
+{
+    if (!e || !e->have_walks || local_walk >= e->w_local) return ~0ull;
+    return local_to_global(*e, local_walk);
+}
+
+int64_t wmh_global_to_local_walk(const wmh_engine* e, uint64_t walk_id) { return e ? global_to_local(*e, walk_id) : -1; }
+
+int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum)
+{
+    if (!e || !sum) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    return guarded([&] {
+        e->bind();
+        auto lc = e->lc();
+        Scratch<unsigned long long> d_sum(e->stream, 1);
+        WHARF_CUDA(cudaMemsetAsync(d_sum.ptr, 0, 8, e->stream));
+        walks_fingerprint(lc, e->walks.ptr, e->w_local, e->walks_L, d_sum.ptr);
+        unsigned long long h = 0;
+        WHARF_CUDA(cudaMemcpyAsync(&h, d_sum.ptr, 8, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        *sum = h;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_build_index(wmh_engine* e)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    return guarded([&] {
+        e->bind();
+        e->index.valid = false;
+        ensure_index(*e);
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_index_find_next(wmh_engine* e, uint32_t vertex, uint64_t walk_id, uint32_t position, uint32_t* next, int* found)
+{
+    if (!e || !next || !found) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    if (vertex >= e->g.n) return fail(WMH_ERR_RANGE, "vertex out of range");
+    const i64 local = global_to_local(*e, walk_id);
+    if (local < 0 || position >= e->walks_L)
+    {
+        *found = 0;
+        *next = kRefSentinel;
+        return WMH_OK;
+    }
+    return guarded([&] {
+        e->bind();
+        ensure_index(*e);
+        auto lc = e->lc();
+        index_find_next(lc, e->index, e->walks.ptr, e->w_local, e->walks_L, vertex, (u64) local, position, e->small.ptr);
+        u32 r[2];
+        WHARF_CUDA(cudaMemcpyAsync(r, e->small.ptr, 8, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        *next = r[0];
+        *found = (int) r[1];
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_index_size(wmh_engine* e, uint32_t vertex, uint64_t* entries)
+{
+    if (!e || !entries) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    if (vertex >= e->g.n) return fail(WMH_ERR_RANGE, "vertex out of range");
+    return guarded([&] {
+        e->bind();
+        ensure_index(*e);
+        u64 p[2];
+        WHARF_CUDA(cudaMemcpyAsync(p, e->index.ptr.ptr + vertex, 16, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        *entries = p[1] - p[0];
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_compressed_walks(wmh_engine* e, uint64_t* ptr, uint64_t* codes, uint64_t capacity, uint64_t* total)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    int rc = guarded([&] {
+        e->bind();
+        try { ensure_codes(*e); }
+        catch (const std::domain_error& d) { return fail(WMH_ERR_DOMAIN, d.what()); }
+        if (total) *total = e->index.entries;
+        if (ptr) WHARF_CUDA(cudaMemcpyAsync(ptr, e->index.ptr.ptr, (e->g.n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+        if (codes)
+        {
+            if (capacity < e->index.entries) return fail(WMH_ERR_RANGE, "code buffer too small");
+            if (e->index.entries) WHARF_CUDA(cudaMemcpyAsync(codes, e->codes.ptr, e->index.entries * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+        }
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+    return rc;
+}
+
+int wmh_compressed_find_next(wmh_engine* e, uint32_t vertex, uint64_t walk_id, uint32_t position, uint32_t* next, int* found)
+{
+    if (!e || !next || !found) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    if (vertex >= e->g.n) return fail(WMH_ERR_RANGE, "vertex out of range");
+    return guarded([&] {
+        e->bind();
+        try { ensure_codes(*e); }
+        catch (const std::domain_error& d) { return fail(WMH_ERR_DOMAIN, d.what()); }
+        u64 p[2];
+        WHARF_CUDA(cudaMemcpyAsync(p, e->index.ptr.ptr + vertex, 16, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        auto lc = e->lc();
+        compressed_find_next(lc, e->codes.ptr + p[0], p[1] - p[0], walk_id, position, e->walks_L, e->small.ptr);
+        u32 r[2];
+        WHARF_CUDA(cudaMemcpyAsync(r, e->small.ptr, 8, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        *next = r[1] ? r[0] : 0xFFFFFFFFu;                // compressed_walks.h:54: next_vertex = -1 when absent
+        *found = (int) r[1];
+        return (int) WMH_OK;
+    });
+}
+
+// ---- Szudzik over device arrays ------------------------------------------------------------------------
+#define WMH_PAIR_OP(body, with_overflow)                                                        \
+    return guarded([&] {                                                                        \
+        DefaultCtx ctx(device);                                                                 \
+        Scratch<unsigned long long> d_over(nullptr, 1);                                         \
+        WHARF_CUDA(cudaMemsetAsync(d_over.ptr, 0, 8, nullptr));                                 \
+        body;                                                                                   \
+        unsigned long long over = 0;                                                            \
+        WHARF_CUDA(cudaMemcpy(&over, d_over.ptr, 8, cudaMemcpyDeviceToHost));                   \
+        if (with_overflow) *(with_overflow) = over;                                             \
+        return (int) WMH_OK;                                                                    \
+    })
+
+int wmh_szudzik_pair_u64(int device, const uint64_t* x, const uint64_t* y, uint64_t* out, uint64_t count, uint64_t* overflow)
+{ WMH_PAIR_OP(szudzik_pair_u64(ctx.lc, x, y, out, count, d_over.ptr), overflow); }
+int wmh_szudzik_unpair_u64(int device, const uint64_t* z, uint64_t* x, uint64_t* y, uint64_t count)
+{ WMH_PAIR_OP(szudzik_unpair_u64(ctx.lc, z, x, y, count), (uint64_t*) nullptr); }
+int wmh_szudzik_pair_u32(int device, const uint32_t* x, const uint32_t* y, uint32_t* out, uint64_t count, uint64_t* overflow)
+{ WMH_PAIR_OP(szudzik_pair_u32(ctx.lc, x, y, out, count, d_over.ptr), overflow); }
+int wmh_szudzik_unpair_u32(int device, const uint32_t* z, uint32_t* x, uint32_t* y, uint64_t count)
+{ WMH_PAIR_OP(szudzik_unpair_u32(ctx.lc, z, x, y, count), (uint64_t*) nullptr); }
+int wmh_szudzik_pair_triplet_u64(int device, const uint64_t* a, const uint64_t* b, const uint64_t* c, uint64_t* out, uint64_t count, uint64_t* overflow)
+{ WMH_PAIR_OP(szudzik_pair_triplet_u64(ctx.lc, a, b, c, out, count, d_over.ptr), overflow); }
+int wmh_szudzik_unpair_triplet_u64(int device, const uint64_t* z, uint64_t* a, uint64_t* b, uint64_t* c, uint64_t count)
+{ WMH_PAIR_OP(szudzik_unpair_triplet_u64(ctx.lc, z, a, b, c, count), (uint64_t*) nullptr); }
+
+uint64_t wmh_szudzik_pair(uint64_t x, uint64_t y) { return szudzik_pair(x, y, nullptr); }
+void wmh_szudzik_unpair(uint64_t z, uint64_t* x, uint64_t* y)
+{
+    u64 a, b;
+    szudzik_unpair(z, &a, &b);
+    if (x) *x = a;
+    if (y) *y = b;
+}
+
+// ---- reporting -----------------------------------------------------------------------------------------
+double wmh_timer_get(const wmh_engine* e, int which) { return (e && which >= 0 && which < 5) ? e->timers[which] : 0.0; }
+void wmh_timer_reset(wmh_engine* e, int which) { if (e && which >= 0 && which < 5) e->timers[which] = 0.0; }
+
+int wmh_memory_footprint(wmh_engine* e, wmh_memory* out)
+{
+    if (!e || !out) return fail(WMH_ERR_INVALID, "null argument");
+    std::memset(out, 0, sizeof(*out));
+    out->graph_bytes = e->g.desc.bytes() + e->g.m * sizeof(u32) + e->g.version.bytes();
+    out->graph_pool_bytes = e->g.pool.bytes() + e->g.memo.bytes();
+    out->walks_bytes = e->have_walks ? e->w_local * e->walks_L * sizeof(u32) : 0;
+    out->index_bytes = e->index.valid ? e->index.ptr.bytes() + e->index.entries * sizeof(u32) + (e->codes_valid ? e->codes.bytes() : 0) : 0;
+    out->scratch_bytes = e->min_pos.bytes() + e->aff_ids.bytes() + e->aff_pos.bytes() + e->bitmap.bytes() + e->touched.bytes() + e->draw.bytes();
+    out->total_bytes = e->g.desc.bytes() + e->g.version.bytes() + out->graph_pool_bytes + e->walks.bytes() + e->index.ptr.bytes() +
+                       e->index.cells.bytes() + e->codes.bytes() + out->scratch_bytes;
+    return WMH_OK;
+}
+
+uint64_t wmh_kernel_launches(const wmh_engine* e) { return e ? e->launches : 0; }
+double wmh_last_walk_kernel_ms(const wmh_engine* e) { return e ? e->last_walk_kernel_ms : 0.0; }
+const uint32_t* wmh_device_walks(const wmh_engine* e) { return (e && e->have_walks) ? e->walks.ptr : nullptr; }
+void* wmh_stream(const wmh_engine* e) { return e ? (void*) e->stream : nullptr; }
+
+int wmh_synchronize(wmh_engine* e)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    return guarded([&] {
+        e->bind();
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_generate_batch_of_edges_device(int device, uint64_t edges_number, uint64_t vertices_number, uint64_t batch_seed, int self_loops,
+                                       int directed, double a, double b, double c, uint32_t* d_out, uint64_t* count)
+{
+    if (!count || (edges_number && !d_out)) return fail(WMH_ERR_INVALID, "null argument");
+    if (vertices_number < 2) return fail(WMH_ERR_INVALID, "vertices_number must be >= 2");
+    if (a + b + c > 1) return fail(WMH_ERR_INVALID, "a + b + c add to more than 1");      // rmat_util.h:16
+    return guarded([&] {
+        DefaultCtx ctx(device);
+        u64 kept = 0;
+        rmat_generate_device(ctx.lc, edges_number, vertices_number, batch_seed, self_loops != 0, directed != 0, a, b, c, d_out, &kept);
+        *count = kept;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_pairs_to_csr_device(int device, uint64_t n, const uint32_t* d_pairs, uint64_t count, uint64_t* d_offsets, uint32_t* d_edges)
+{
+    if (!d_offsets || (count && (!d_pairs || !d_edges))) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        DefaultCtx ctx(device);
+        pairs_to_csr_device(ctx.lc, n, d_pairs, count, d_offsets, d_edges);
+        WHARF_CUDA(cudaStreamSynchronize(nullptr));
+        return (int) WMH_OK;
+    });
+}
+
+}  // extern "C"

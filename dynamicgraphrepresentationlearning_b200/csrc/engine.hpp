@@ -1,0 +1,153 @@
+// Host-side engine state and the launch wrappers implemented by the kernel translation units.
+#pragma once
+
+#include "common.cuh"
+#include "../../include/wharfmh_b200.h"
+
+#include <vector>
+
+namespace wharf
+{
+struct LaunchCtx
+{
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    u64* launches = nullptr;      // hand-written kernel launches
+    u64* library_calls = nullptr; // CUB device-wide algorithm invocations
+    void count(u64 k = 1) const { if (launches) *launches += k; }
+    void count_lib(u64 k = 1) const { if (library_calls) *library_calls += k; }
+};
+
+// Stream-ordered scratch allocation (cudaMallocAsync), released at scope exit.
+template <class T>
+struct Scratch
+{
+    T* ptr = nullptr;
+    u64 count = 0;
+    cudaStream_t stream = nullptr;
+    Scratch() = default;
+    Scratch(cudaStream_t s, u64 n) { allocate(s, n); }
+    Scratch(const Scratch&) = delete;
+    Scratch& operator=(const Scratch&) = delete;
+    Scratch(Scratch&& o) noexcept : ptr(o.ptr), count(o.count), stream(o.stream) { o.ptr = nullptr; }
+    Scratch& operator=(Scratch&& o) noexcept
+    {
+        if (this != &o) { release(); ptr = o.ptr; count = o.count; stream = o.stream; o.ptr = nullptr; }
+        return *this;
+    }
+    ~Scratch() { release(); }
+    void allocate(cudaStream_t s, u64 n)
+    {
+        release();
+        stream = s;
+        count = n;
+        cudaError_t e = cudaMallocAsync((void**) &ptr, (n ? n : 1) * sizeof(T), s);
+        if (e != cudaSuccess)
+        {
+            ptr = nullptr;
+            cudaGetLastError();
+            throw CudaError(e, "cudaMallocAsync of " + std::to_string(n * sizeof(T)) + " bytes failed: " + cudaGetErrorString(e));
+        }
+    }
+    void release()
+    {
+        if (ptr) cudaFreeAsync(ptr, stream);
+        ptr = nullptr;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Device adjacency: row descriptors + append-only neighbour pool (graph/snapshot.h FlatGraph on device).
+// ------------------------------------------------------------------------------------------------
+struct DeviceGraph
+{
+    u64 n = 0;                       // number_of_vertices()
+    u64 m = 0;                       // number_of_edges() (directed entries)
+    DeviceBuffer<RowDesc> desc;      // n
+    DeviceBuffer<u32> pool;          // neighbour pool, rows ascending & unique
+    u64 pool_used = 0;               // elements of pool handed out (live + garbage)
+    DeviceBuffer<u32> version;       // n: sampler-manager generation per vertex (graph/vertex.h:12)
+    DeviceBuffer<u32> memo;          // optional, aligned with pool: cached sampler init value per edge cur->prev
+};
+
+// One prepared edge batch (sorted, deduplicated) and what the merge learned about it.
+struct PreparedBatch
+{
+    u64 k = 0;                       // unique (src,dst) keys
+    u64 n_sources = 0;               // distinct sources
+    Scratch<u64> keys;               // k      : (src << 32) | dst, ascending
+    Scratch<u32> sources;            // n_src  : distinct sources ascending
+    Scratch<u64> slice;              // n_src+1: batch slice of each source in keys
+};
+
+// ---- graph kernels (kernels_graph.cu) -------------------------------------------------------------
+void graph_build_desc(const LaunchCtx& lc, const u64* d_offsets_n, u64 n, u64 m, RowDesc* d_desc);
+void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, bool drop_self_loops, u64 n,
+                         PreparedBatch& out, u32* d_sorted_pairs_out /* nullable: count pairs, sorted (not deduped) */);
+// Applies the batch; returns the pool elements appended. Updates g.m, g.pool_used, version[], touched bitmap.
+void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch& b, bool is_delete, u32* d_touched_bitmap);
+void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity);
+void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr /* n+1 */, u32* d_col /* m */);
+void graph_check_ids(const LaunchCtx& lc, const u32* d_pairs, u64 count, u64 n, u32* d_flag);
+void rmat_generate_device(const LaunchCtx& lc, u64 edges_number, u64 vertices_number, u64 batch_seed, bool self_loops,
+                          bool directed, double a, double b, double c, u32* d_out, u64* count_out);
+void pairs_to_csr_device(const LaunchCtx& lc, u64 n, const u32* d_pairs, u64 count, u64* d_offsets, u32* d_edges);
+
+// ---- walk kernels (kernels_walk.cu) ---------------------------------------------------------------
+struct WalkParams
+{
+    const RowDesc* desc = nullptr;
+    const u32* pool = nullptr;
+    const u32* version = nullptr;
+    u32* memo = nullptr;             // sampler-state cache aligned with pool (MH node2vec), kNoVertex = empty
+    const u64* draw = nullptr;       // X[wpv][L]
+    u32* walks = nullptr;            // [L][W_local] position-major
+    u64 n = 0;                       // global vertices
+    u64 w_local = 0;                 // local walks
+    u32 n_local = 0;                 // local start vertices
+    u32 wpv = 0, L = 0;
+    u32 rank = 0, world = 1;
+    u32 model = 0, deterministic = 1, init_strategy = 2;
+    float p = 1.f, q = 1.f;
+    u64 seed = 0;
+};
+void walks_generate(const LaunchCtx& lc, const WalkParams& wp, unsigned long long* d_steps);
+void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affected, const u32* d_positions, u64 count,
+                  unsigned long long* d_steps);
+// min_pos[w] = first position whose vertex is in the touched bitmap (kNoPos when none).
+void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_bitmap, u32* d_min_pos);
+// Compacts min_pos != kNoPos into (ids, positions); returns the count.
+u64  walks_compact_affected(const LaunchCtx& lc, const u32* d_min_pos, u64 w_local, u32* d_ids, u32* d_positions);
+void walks_transpose_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 first, u64 count, u32* d_out);
+void walks_gather_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_ids, u64 count, u32* d_out);
+void walks_fingerprint(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, unsigned long long* d_sum);
+void fill_u32(const LaunchCtx& lc, u32* d, u64 count, u32 value);
+
+// ---- index kernels (kernels_index.cu) -------------------------------------------------------------
+struct DeviceIndex
+{
+    bool valid = false;
+    u64 entries = 0;                 // stored steps (walk matrix cells holding a vertex)
+    DeviceBuffer<u64> ptr;           // n+1: segment of each vertex in `cells`
+    DeviceBuffer<u32> cells;         // flat cell id = position * W_local + local_walk, ascending per vertex
+};
+void index_build(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 n, DeviceIndex& idx);
+// atomicMin of the position of every index entry of every source into min_pos; returns entries visited.
+u64  index_search(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_sources, u64 n_sources, u64 w_local, u32* d_min_pos);
+u64  index_count_touched(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_sources, u64 n_sources);
+void index_find_next(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u32 vertex,
+                     u64 local_walk, u32 position, u32* d_out2 /* [next, found] */);
+void compressed_walks_encode(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u64 n,
+                             u32 n_local, u32 rank, u32 world, u64* d_codes);
+void compressed_find_next(const LaunchCtx& lc, const u64* d_codes, u64 count, u64 walk_id, u32 position, u32 L, u32* d_out2);
+
+// ---- pairing kernels (kernels_pairings.cu) --------------------------------------------------------
+void szudzik_pair_u64(const LaunchCtx& lc, const u64* x, const u64* y, u64* out, u64 count, unsigned long long* d_overflow);
+void szudzik_unpair_u64(const LaunchCtx& lc, const u64* z, u64* x, u64* y, u64 count);
+void szudzik_pair_u32(const LaunchCtx& lc, const u32* x, const u32* y, u32* out, u64 count, unsigned long long* d_overflow);
+void szudzik_unpair_u32(const LaunchCtx& lc, const u32* z, u32* x, u32* y, u64 count);
+void szudzik_pair_triplet_u64(const LaunchCtx& lc, const u64* a, const u64* b, const u64* c, u64* out, u64 count,
+                              unsigned long long* d_overflow);
+void szudzik_unpair_triplet_u64(const LaunchCtx& lc, const u64* z, u64* a, u64* b, u64* c, u64 count);
+
+}  // namespace wharf

@@ -1,0 +1,442 @@
+// Walk kernels: bulk generation, re-walk of affected walks, corpus scan, retrieval.
+//
+// Replaces graph/wharfmh.h:275-326 (generate_initial_random_walks hot loop A), :761-859
+// (batch_walk_update insert_job), walks/models/{deepwalk,node2vec}.h, walks/metropolis_hastings_sampler.h
+// and the retrieval of :365-427.
+//
+// Layout: the corpus is a position-major matrix walks[L][W_local] of u32 vertex ids, so that the
+// one-walker-per-thread kernels store fully coalesced (lane i writes walks[pos][w0 + i]); a walker that
+// stopped (isolated start / sink) leaves kNoVertex in the remaining cells.
+#include "engine.hpp"
+#include "rng.cuh"
+
+#include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+
+namespace wharf
+{
+namespace
+{
+constexpr int kWalkBlock = 256;
+
+struct DevWalkParams
+{
+    const RowDesc* __restrict__ desc;
+    const u32* __restrict__ pool;
+    const u32* __restrict__ version;
+    u32* memo;                        // sampler-state cache aligned with pool (MH node2vec)
+    const u64* __restrict__ draw;
+    u32* walks;
+    u64 n;
+    u64 w_local;
+    u32 n_local;
+    u32 L;
+    u32 rank, world;
+    u32 init_strategy;
+    float inv_p, inv_q;
+    u64 seed;
+};
+
+__device__ __forceinline__ RowDesc load_desc(const RowDesc* __restrict__ desc, u32 v)
+{
+    const uint2 t = __ldg(reinterpret_cast<const uint2*>(desc) + v);
+    return RowDesc{t.x, t.y};
+}
+
+// ---- deterministic rule (graph/wharfmh.h:304-309, :836-838) ----------------------------------------
+// next = N(cur)[ X[walk_id / n][pos - start_pos] % deg(cur) ]
+//
+// kRewalk = false: thread t owns local walk t, starts at position 0 on its start vertex.
+// kRewalk = true : thread t owns affected[t], resumes at positions[t] on the vertex stored there.
+template <bool kRewalk>
+__global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkParams p, const u32* __restrict__ affected,
+                                                                        const u32* __restrict__ positions, u64 count,
+                                                                        unsigned long long* steps_out)
+{
+    const u64 t = (u64) blockIdx.x * kWalkBlock + threadIdx.x;
+    u32 steps = 0;
+    if (t < count)
+    {
+        u64 w;
+        u32 pos, cur;
+        if (kRewalk)
+        {
+            w   = __ldg(affected + t);
+            pos = __ldg(positions + t);
+            cur = p.walks[(u64) pos * p.w_local + w];
+        }
+        else
+        {
+            w   = t;
+            pos = 0;
+        }
+        const u32 replica = (u32) (w / p.n_local);                  // = walk_id / n  (wharfmh.h:291)
+        if (!kRewalk)
+        {
+            cur = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;   // = walk_id % n (wharfmh.h:292)
+            p.walks[w] = cur;
+        }
+        const u64* __restrict__ X = p.draw + (u64) replica * p.L;   // stream restarts at the re-walk point (:814-816)
+        u32* out = p.walks + (u64) (pos + 1) * p.w_local + w;
+        const u32 first = pos;
+        const u32 last = p.L - 1;
+        bool stopped = false;
+        for (; pos < last; ++pos, out += p.w_local)
+        {
+            const RowDesc d = load_desc(p.desc, cur);
+            if (d.degree == 0) { stopped = true; break; }            // isolated start (:277-286) or sink
+            const u32 j = mod_u64_u32(__ldg(X + (pos - first)), d.degree);
+            cur = __ldg(p.pool + d.begin + j);
+            *out = cur;
+        }
+        if (first == last) stopped = load_desc(p.desc, cur).degree == 0;   // resumed on the last cell: only the degree matters
+        steps = pos - first + (stopped ? 0u : 1u);                   // the draw at the last position is unobservable (:315-317)
+        for (++pos; pos <= last; ++pos, out += p.w_local) *out = kNoVertex;
+    }
+    block_add_u64(steps_out, steps);
+}
+
+// ---- Metropolis-Hastings mode ------------------------------------------------------------------------
+
+__device__ __forceinline__ bool row_contains(const u32* __restrict__ pool, RowDesc d, u32 key, u32* index)
+{
+    const u32 i = lower_bound_u32(pool + d.begin, d.degree, key);      // node2vec.h:112-119 (std::binary_search)
+    *index = i;
+    return i < d.degree && __ldg(pool + d.begin + i) == key;
+}
+
+// Node2Vec::weight - walks/models/node2vec.h:74-88; state = (cur, prev), dprev = row of prev.
+__device__ __forceinline__ float n2v_weight(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x)
+{
+    if (x == prev) return p.inv_p;
+    u32 ignore;
+    return row_contains(p.pool, dprev, x, &ignore) ? 1.0f : p.inv_q;
+}
+
+// MetropolisHastingsSampler::accept - walks/metropolis_hastings_sampler.h:118-122.
+__device__ __forceinline__ bool mh_accept(float w_old, float w_new, u64 draw)
+{
+    if (w_old < w_new) return true;
+    return unit_double(draw) <= (double) w_new / (double) w_old;
+}
+
+// MetropolisHastingsSampler::init - walks/metropolis_hastings_sampler.h:69-108, draws keyed by
+// (seed, cur, prev, version[cur], i).
+__device__ u32 n2v_sampler_init(const DevWalkParams& p, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
+{
+    const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
+    u64 i = 0;
+    const u32* __restrict__ nb = p.pool + dcur.begin;
+    u32 last = __ldg(nb + mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree));   // RANDOM :72-75
+    if (p.init_strategy == WMH_INIT_BURNIN)                                                               // :77-85
+    {
+        for (int it = 0; it < 100; it++)
+        {
+            const u32 cand = __ldg(nb + mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree));
+            const float wn = n2v_weight(p, prev, dprev, cand), wo = n2v_weight(p, prev, dprev, last);
+            bool acc = wo < wn;
+            if (!acc) acc = unit_double(keyed_draw(p.seed, kDomSampler, cur, key_b, i++)) <= (double) wn / (double) wo;
+            if (acc) last = cand;
+        }
+    }
+    else if (p.init_strategy == WMH_INIT_WEIGHT)                                                          // :87-107
+    {
+        u32 best = last;
+        float best_w = n2v_weight(p, prev, dprev, best);
+        for (int it = 0; it < 20; it++)
+        {
+            const u32 cand = __ldg(nb + mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree));
+            const float w = n2v_weight(p, prev, dprev, cand);
+            if (w > best_w) { best_w = w; best = cand; }
+        }
+        last = best;
+    }
+    return last;
+}
+
+// kModel: WMH_DEEPWALK / WMH_NODE2VEC.  One walker per thread; the prev-neighbour test is a per-thread
+// binary search over the ascending row of prev.
+template <int kModel, bool kRewalk>
+__global__ void __launch_bounds__(kWalkBlock) walk_mh_kernel(DevWalkParams p, const u32* __restrict__ affected,
+                                                             const u32* __restrict__ positions, u64 count,
+                                                             unsigned long long* steps_out)
+{
+    const u64 t = (u64) blockIdx.x * kWalkBlock + threadIdx.x;
+    u32 steps = 0;
+    if (t < count)
+    {
+        u64 w;
+        u32 pos = 0, cur, prev;
+        if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = t; }
+        const u32 replica = (u32) (w / p.n_local);
+        const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
+        const u64 walk_id = (u64) replica * p.n + start;             // global id keys the draws
+        if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
+        else { cur = start; p.walks[w] = cur; }
+        prev = cur;
+        if (kModel == WMH_NODE2VEC)
+        {
+            if (pos > 0) prev = p.walks[(u64) (pos - 1) * p.w_local + w];                 // wharfmh.h:819-823
+            else
+            {
+                const RowDesc d0 = load_desc(p.desc, cur);                                 // node2vec.h:42-49
+                if (d0.degree) prev = __ldg(p.pool + d0.begin + mod_u64_u32(keyed_draw(p.seed, kDomState, walk_id, 0, 0), d0.degree));
+            }
+        }
+        u32* out = p.walks + (u64) (pos + 1) * p.w_local + w;
+        const u32 first = pos;
+        const u32 last_pos = p.L - 1;
+        bool stopped = false;
+        for (; pos < last_pos; ++pos, out += p.w_local)
+        {
+            const RowDesc d = load_desc(p.desc, cur);
+            if (d.degree == 0) { stopped = true; break; }
+            // propose_vertex - deepwalk.h:79-87 / node2vec.h:97-105
+            const u32 cand = __ldg(p.pool + d.begin + mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree));
+            u32 next;
+            if (kModel == WMH_DEEPWALK)
+            {
+                next = cand;               // weight == 1 (deepwalk.h:67-70): accept() is drand() <= 1.0, always true
+            }
+            else
+            {
+                const RowDesc dprev = load_desc(p.desc, prev);
+                // The sampler of state (cur, prev) lives in cur's SamplerManager (graph/vertex.h:12) and, because
+                // find() hands out copies (wharfmh.h:301,833), never advances past its init value: cache that
+                // value in the slot of edge cur->prev.  A re-written row starts with an empty cache, which is the
+                // reset of wharfmh.h:504->539.
+                u32 slot_index;
+                const bool has_slot = row_contains(p.pool, d, prev, &slot_index);
+                u32 last = kNoVertex;
+                if (has_slot) last = __ldcg(p.memo + d.begin + slot_index);
+                if (last == kNoVertex)
+                {
+                    last = n2v_sampler_init(p, cur, d, prev, dprev);
+                    if (has_slot) __stcg(p.memo + d.begin + slot_index, last);
+                }
+                const float wn = n2v_weight(p, prev, dprev, cand);                         // sample :31-46
+                const float wo = n2v_weight(p, prev, dprev, last);
+                bool acc = wo < wn;
+                if (!acc) acc = unit_double(keyed_draw(p.seed, kDomStep, walk_id, pos, 1)) <= (double) wn / (double) wo;
+                next = acc ? cand : last;
+            }
+            *out = next;
+            prev = cur;
+            cur = next;
+        }
+        if (first == last_pos) stopped = load_desc(p.desc, cur).degree == 0;
+        steps = pos - first + (stopped ? 0u : 1u);
+        for (++pos; pos <= last_pos; ++pos, out += p.w_local) *out = kNoVertex;
+    }
+    block_add_u64(steps_out, steps);
+}
+
+// ---- corpus scan: earliest position standing on a touched vertex (MapOfChanges, wharfmh.h:519-537) ----
+__global__ void __launch_bounds__(256) scan_touched_kernel(const u32* __restrict__ walks, u64 w_local, u32 L,
+                                                            const u32* __restrict__ bitmap, u32* __restrict__ min_pos)
+{
+    const u64 w = (u64) blockIdx.x * 256 + threadIdx.x;
+    if (w >= w_local) return;
+    const u32* col = walks + w;
+    u32 found = kNoPos;
+    // positions in chunks of 8 independent coalesced loads, then test in order
+    for (u32 base = 0; base < L && found == kNoPos; base += 8)
+    {
+        u32 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = (base + i < L) ? __ldcs(col + (u64) (base + i) * w_local) : kNoVertex;
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+        {
+            if (found != kNoPos) break;
+            if (v[i] == kNoVertex) { base = L; break; }                  // walker stopped: nothing further
+            if ((__ldg(bitmap + (v[i] >> 5)) >> (v[i] & 31)) & 1u) found = base + i;
+        }
+    }
+    min_pos[w] = found;
+}
+
+struct IsAffected
+{
+    const u32* min_pos;
+    __device__ bool operator()(u32 w) const { return min_pos[w] != kNoPos; }
+};
+
+__global__ void gather_positions_kernel(const u32* __restrict__ min_pos, const u32* __restrict__ ids, u64 count, u32* __restrict__ positions)
+{
+    const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) positions[i] = min_pos[ids[i]];
+}
+
+// ---- retrieval -----------------------------------------------------------------------------------------
+// Tile transpose [L][W] -> rows [count][L] for local walks first..first+count.
+__global__ void __launch_bounds__(256) transpose_rows_kernel(const u32* __restrict__ walks, u64 w_local, u32 L, u64 first, u64 count,
+                                                              u32* __restrict__ out)
+{
+    __shared__ u32 tile[32][33];
+    const u64 w0 = (u64) blockIdx.x * 32;
+    const u32 p0 = blockIdx.y * 32;
+    const u32 tx = threadIdx.x & 31, ty = threadIdx.x >> 5;          // 32 x 8
+    for (u32 r = ty; r < 32; r += 8)
+    {
+        const u32 pos = p0 + r;
+        const u64 w = w0 + tx;
+        tile[r][tx] = (pos < L && w < count) ? walks[(u64) pos * w_local + first + w] : kNoVertex;
+    }
+    __syncthreads();
+    for (u32 r = ty; r < 32; r += 8)
+    {
+        const u64 w = w0 + r;
+        const u32 pos = p0 + tx;
+        if (w < count && pos < L) out[w * L + pos] = tile[tx][r];
+    }
+}
+
+__global__ void gather_rows_kernel(const u32* __restrict__ walks, u64 w_local, u32 L, const u32* __restrict__ ids, u64 count,
+                                   u32* __restrict__ out)
+{
+    // one warp per walk, lanes over positions
+    const u64 warp = ((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 lane = threadIdx.x & 31;
+    if (warp >= count) return;
+    const u64 w = ids[warp];
+    for (u32 pos = lane; pos < L; pos += 32) out[warp * L + pos] = walks[(u64) pos * w_local + w];
+}
+
+// Sum over walks of the FNV-1a-64 of each walk's text form "v0 v1 ... " (graph/wharfmh.h:365-394).
+__global__ void __launch_bounds__(256) fingerprint_kernel(const u32* __restrict__ walks, u64 w_local, u32 L, unsigned long long* sum)
+{
+    const u64 w = (u64) blockIdx.x * 256 + threadIdx.x;
+    u64 h = 0;
+    if (w < w_local)
+    {
+        h = 0xcbf29ce484222325ull;
+        for (u32 pos = 0; pos < L; pos++)
+        {
+            u32 v = walks[(u64) pos * w_local + w];
+            if (v == kNoVertex) break;
+            char buf[10];
+            int len = 0;
+            do { buf[len++] = (char) ('0' + v % 10); v /= 10; } while (v);
+            while (len) { h ^= (u8) buf[--len]; h *= 0x100000001b3ull; }
+            h ^= (u8) ' ';
+            h *= 0x100000001b3ull;
+        }
+    }
+    // wrapping 64-bit sum: warp reduce then one atomic per warp
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
+    if ((threadIdx.x & 31) == 0 && h) atomicAdd(sum, (unsigned long long) h);
+}
+
+__global__ void fill_u32_kernel(u32* __restrict__ d, u64 count, u32 value)
+{
+    for (u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (u64) gridDim.x * blockDim.x) d[i] = value;
+}
+
+DevWalkParams to_dev(const WalkParams& wp)
+{
+    DevWalkParams p;
+    p.desc = wp.desc; p.pool = wp.pool; p.version = wp.version; p.memo = wp.memo; p.draw = wp.draw; p.walks = wp.walks;
+    p.n = wp.n; p.w_local = wp.w_local; p.n_local = wp.n_local; p.L = wp.L; p.rank = wp.rank; p.world = wp.world;
+    p.init_strategy = wp.init_strategy;
+    p.inv_p = 1 / wp.p;                                                 // node2vec.h:78
+    p.inv_q = 1 / wp.q;                                                 // node2vec.h:86
+    p.seed = wp.seed;
+    return p;
+}
+
+template <bool kRewalk>
+void launch_walk(const LaunchCtx& lc, const WalkParams& wp, const u32* ids, const u32* positions, u64 count, unsigned long long* d_steps)
+{
+    if (count == 0) return;
+    const DevWalkParams p = to_dev(wp);
+    const unsigned grid = div_up(count, kWalkBlock);
+    if (wp.deterministic)
+        walk_deterministic_kernel<kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
+    else if (wp.model == WMH_NODE2VEC)
+        walk_mh_kernel<WMH_NODE2VEC, kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
+    else
+        walk_mh_kernel<WMH_DEEPWALK, kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+}  // namespace
+
+void walks_generate(const LaunchCtx& lc, const WalkParams& wp, unsigned long long* d_steps)
+{
+    launch_walk<false>(lc, wp, nullptr, nullptr, wp.w_local, d_steps);
+}
+
+void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affected, const u32* d_positions, u64 count,
+                  unsigned long long* d_steps)
+{
+    launch_walk<true>(lc, wp, d_affected, d_positions, count, d_steps);
+}
+
+void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_bitmap, u32* d_min_pos)
+{
+    if (w_local == 0) return;
+    scan_touched_kernel<<<div_up(w_local, 256), 256, 0, lc.stream>>>(d_walks, w_local, L, d_bitmap, d_min_pos);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+u64 walks_compact_affected(const LaunchCtx& lc, const u32* d_min_pos, u64 w_local, u32* d_ids, u32* d_positions)
+{
+    if (w_local == 0) return 0;
+    Scratch<u64> d_count(lc.stream, 1);
+    cub::CountingInputIterator<u32> iota(0);
+    IsAffected pred{d_min_pos};
+    size_t temp_bytes = 0;
+    WHARF_CUDA(cub::DeviceSelect::If(nullptr, temp_bytes, iota, d_ids, d_count.ptr, (i64) w_local, pred, lc.stream));
+    Scratch<u8> temp(lc.stream, temp_bytes);
+    WHARF_CUDA(cub::DeviceSelect::If(temp.ptr, temp_bytes, iota, d_ids, d_count.ptr, (i64) w_local, pred, lc.stream));
+    lc.count_lib();
+    u64 count = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&count, d_count.ptr, sizeof(u64), cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
+    if (count)
+    {
+        gather_positions_kernel<<<div_up(count, 256), 256, 0, lc.stream>>>(d_min_pos, d_ids, count, d_positions);
+        lc.count();
+        WHARF_CUDA(cudaGetLastError());
+    }
+    return count;
+}
+
+void walks_transpose_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 first, u64 count, u32* d_out)
+{
+    if (count == 0) return;
+    dim3 grid(div_up(count, 32), div_up(L, 32));
+    transpose_rows_kernel<<<grid, 256, 0, lc.stream>>>(d_walks, w_local, L, first, count, d_out);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void walks_gather_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_ids, u64 count, u32* d_out)
+{
+    if (count == 0) return;
+    gather_rows_kernel<<<div_up(count * 32, 256), 256, 0, lc.stream>>>(d_walks, w_local, L, d_ids, count, d_out);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void walks_fingerprint(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, unsigned long long* d_sum)
+{
+    if (w_local == 0) return;
+    fingerprint_kernel<<<div_up(w_local, 256), 256, 0, lc.stream>>>(d_walks, w_local, L, d_sum);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void fill_u32(const LaunchCtx& lc, u32* d, u64 count, u32 value)
+{
+    if (count == 0) return;
+    fill_u32_kernel<<<grid_for(count, 256, 8, lc.sm_count), 256, 0, lc.stream>>>(d, count, value);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+}  // namespace wharf

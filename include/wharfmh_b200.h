@@ -1,0 +1,254 @@
+/*
+ * wharfmh_b200.h - C ABI of the B200-native WharfMH hot path (libwharfmh_b200.so).
+ *
+ * Drop-in boundary: the reference has no FFI; its boundary is the public C++ surface of
+ * dygrl::WharfMH (graph/wharfmh.h:21) plus the mutable globals of namespace config
+ * (config/globals.h:7-29).  Each entry point below names the reference member it replaces
+ * (file:line relative to the reference root).  include/wharfmh_b200.hpp rebuilds the C++ class on top
+ * of these functions; INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every function returns a wmh_status (0 = OK) unless noted;
+ *     wmh_last_error() returns the message of the last failure on the calling thread
+ *     (reference: std::exit(1) / abort() / exceptions / SIGFPE).
+ *   - one host thread drives one engine; an engine owns one CUDA stream on one device
+ *     (reference: process-global state, one engine per process).
+ *   - `host` pointers are ordinary (pageable or pinned) host memory; `_device` variants take device
+ *     pointers on the engine's device and never touch the host.
+ *   - walk ids are GLOBAL ids (walk_id = replica * n + start_vertex, graph/wharfmh.h:275-292); with
+ *     world > 1 an engine owns the walks whose start vertex satisfies start % world == rank, the graph
+ *     is replicated.
+ *   - there is no CPU fallback: every call fails with WMH_ERR_CUDA when no sm_100-class device is usable.
+ */
+#ifndef WHARFMH_B200_H
+#define WHARFMH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WMH_API __attribute__((visibility("default")))
+
+/* Vertex value used for "no vertex" in retrieved walks (positions after a walker stopped). */
+#define WMH_NO_VERTEX 0xFFFFFFFFu
+/* The reference's end-of-walk sentinel as stored in its index (graph/wharfmh.h:283,317). */
+#define WMH_REF_SENTINEL 0xFFFFFFFEu
+
+typedef enum
+{
+    WMH_OK = 0,
+    WMH_ERR_INVALID = 1,      /* bad argument (null pointer, id >= n, walk_length == 0 ...) */
+    WMH_ERR_CUDA = 2,         /* CUDA runtime failure or no usable device */
+    WMH_ERR_OOM = 3,          /* device allocation failed */
+    WMH_ERR_STATE = 4,        /* call not valid in the current state (e.g. walks not generated yet) */
+    WMH_ERR_DOMAIN = 5,       /* value outside the representable domain (pairing overflow, > 2^32 pool) */
+    WMH_ERR_RANGE = 6         /* caller buffer too small / id out of range */
+} wmh_status;
+
+/* types::RandomWalkModelType (config/types.h:31) */
+typedef enum { WMH_DEEPWALK = 0, WMH_NODE2VEC = 1 } wmh_model;
+/* types::SamplerInitStartegy (config/types.h:34) */
+typedef enum { WMH_INIT_RANDOM = 0, WMH_INIT_BURNIN = 1, WMH_INIT_WEIGHT = 2 } wmh_sampler_init;
+/* How affected walks are found after an edge batch (walks/inverted_index.h + graph/wharfmh.h:519-537). */
+typedef enum
+{
+    WMH_SEARCH_AUTO = 0,      /* index when few index entries are touched, corpus scan otherwise */
+    WMH_SEARCH_INDEX = 1,     /* device radix-sorted inverted index + segmented search */
+    WMH_SEARCH_SCAN = 2       /* stream the walk matrix against the touched-vertex bitmap */
+} wmh_search_mode;
+
+/* The knobs of namespace config (config/globals.h:7-29) plus placement.  Read at call time, like the
+ * reference reads its globals (graph/wharfmh.h:254-272). */
+typedef struct
+{
+    uint32_t walks_per_vertex;   /* config::walks_per_vertex (uint8_t in the reference: 1..255) */
+    uint32_t walk_length;        /* config::walk_length      (uint8_t in the reference: 1..255) */
+    uint32_t model;              /* wmh_model: config::random_walk_model */
+    uint32_t deterministic;      /* config::deterministic_mode: 1 = per-walk xoroshiro stream, bit-exact vs reference */
+    float    param_p;            /* config::paramP */
+    float    param_q;            /* config::paramQ */
+    uint32_t init_strategy;      /* wmh_sampler_init: config::sampler_init_strategy */
+    uint32_t search_mode;        /* wmh_search_mode */
+    uint64_t seed;               /* keyed-MH seed (reference: utility::Random(std::time(nullptr)), config/globals.h:26) */
+    int32_t  device;             /* CUDA device ordinal */
+    uint32_t rank;               /* shard of the walk corpus owned by this engine */
+    uint32_t world;              /* number of shards (>= 1) */
+    uint32_t reserved;
+} wmh_config;
+
+typedef struct wmh_engine wmh_engine;
+
+/* Device-memory accounting: the counterpart of WharfMH::memory_footprint (graph/wharfmh.h:928-998). */
+typedef struct
+{
+    uint64_t graph_bytes;        /* row descriptors + neighbour pool (in use) */
+    uint64_t graph_pool_bytes;   /* neighbour pool capacity */
+    uint64_t walks_bytes;        /* position-major walk matrix */
+    uint64_t index_bytes;        /* inverted index (0 when not built) */
+    uint64_t scratch_bytes;      /* per-batch scratch currently held */
+    uint64_t total_bytes;
+} wmh_memory;
+
+/* The four global timers of config/config.h:10-14, in seconds, accumulated since the last reset. */
+typedef enum
+{
+    WMH_TIMER_GRAPH_UPDATE_INSERT = 0,
+    WMH_TIMER_WALK_UPDATE_INSERT = 1,
+    WMH_TIMER_GRAPH_UPDATE_DELETE = 2,
+    WMH_TIMER_WALK_UPDATE_DELETE = 3,
+    WMH_TIMER_GENERATE = 4        /* device time of the last generate_initial_random_walks */
+} wmh_timer;
+
+/* ---- lifecycle ---------------------------------------------------------------------------------- */
+
+WMH_API void wmh_default_config(wmh_config* cfg);                        /* config/globals.h defaults */
+WMH_API const char* wmh_last_error(void);
+WMH_API const char* wmh_version(void);
+
+/* WharfMH(long n, long m, uintE* offsets, uintV* edges, bool free_memory) - graph/wharfmh.h:58.
+ * `offsets` has n entries (no n+1-th; the last degree is m - offsets[n-1], wharfmh.h:74-75); rows must be
+ * sorted and unique.  The arrays are copied, never freed (the C++ shim frees them when free_memory). */
+WMH_API int wmh_create(wmh_engine** out, uint64_t n, uint64_t m, const uint64_t* offsets, const uint32_t* edges,
+                       const wmh_config* cfg);
+/* Same, CSR already resident on the engine's device. */
+WMH_API int wmh_create_device(wmh_engine** out, uint64_t n, uint64_t m, const uint64_t* d_offsets,
+                              const uint32_t* d_edges, const wmh_config* cfg);
+/* WharfMH(long n, long m) - graph/wharfmh.h:26: n isolated vertices. */
+WMH_API int wmh_create_empty(wmh_engine** out, uint64_t n, const wmh_config* cfg);
+/* WharfMH::destroy - graph/wharfmh.h:228 (also releases the handle). */
+WMH_API void wmh_destroy(wmh_engine* e);
+/* WharfMH::destroy_index - graph/wharfmh.h:237: drops the walk corpus and its inverted index. */
+WMH_API int wmh_destroy_index(wmh_engine* e);
+/* Assigning config::* between calls (experiments/src/throughput-latency.cpp:19-75). */
+WMH_API int wmh_set_config(wmh_engine* e, const wmh_config* cfg);
+WMH_API int wmh_get_config(const wmh_engine* e, wmh_config* cfg);
+
+/* ---- graph -------------------------------------------------------------------------------------- */
+
+WMH_API uint64_t wmh_number_of_vertices(const wmh_engine* e);            /* graph/wharfmh.h:117 */
+WMH_API uint64_t wmh_number_of_edges(const wmh_engine* e);               /* graph/wharfmh.h:130 */
+/* WharfMH::flatten_graph - graph/wharfmh.h:175 / FlatGraph (graph/snapshot.h:108-194):
+ * row_ptr has n+1 entries, col has number_of_edges() entries, rows ascending. */
+WMH_API int wmh_flatten_graph(wmh_engine* e, uint64_t* row_ptr, uint32_t* col);
+WMH_API int wmh_degree(wmh_engine* e, uint32_t vertex, uint64_t* degree);
+WMH_API int wmh_neighbors(wmh_engine* e, uint32_t vertex, uint32_t* out, uint64_t capacity, uint64_t* degree);
+
+/* ---- walks -------------------------------------------------------------------------------------- */
+
+/* WharfMH::generate_initial_random_walks - graph/wharfmh.h:250. */
+WMH_API int wmh_generate_initial_random_walks(wmh_engine* e);
+/* Walker steps executed by the last generate / batch update (a step = one iteration of wharfmh.h:294). */
+WMH_API uint64_t wmh_last_steps(const wmh_engine* e);
+WMH_API uint64_t wmh_number_of_walks(const wmh_engine* e);               /* global: n * walks_per_vertex */
+WMH_API uint64_t wmh_number_of_local_walks(const wmh_engine* e);         /* owned by this rank */
+
+/* WharfMH::insert_edges_batch / delete_edges_batch - graph/wharfmh.h:439 / 588.
+ * `edges` = m pairs (src, dst) in host memory.  When !sorted the caller's array is sorted in place by
+ * (src, dst), as the reference does (wharfmh.h:452).  remove_dups also drops self-loops (wharfmh.h:456-470).
+ * `nn` is accepted for signature parity (sort-key width in the reference) and ignored.
+ * *n_affected receives the number of affected walks owned by this rank; fetch them with wmh_affected_walks. */
+WMH_API int wmh_insert_edges_batch(wmh_engine* e, uint64_t m, uint32_t* edges, int sorted, int remove_dups,
+                                   uint64_t nn, int apply_walk_updates, uint64_t* n_affected);
+WMH_API int wmh_delete_edges_batch(wmh_engine* e, uint64_t m, uint32_t* edges, int sorted, int remove_dups,
+                                   uint64_t nn, int apply_walk_updates, uint64_t* n_affected);
+/* Same with the batch resident on the device (read-only; not sorted in place). */
+WMH_API int wmh_insert_edges_batch_device(wmh_engine* e, uint64_t m, const uint32_t* d_edges, int remove_dups,
+                                          int apply_walk_updates, uint64_t* n_affected);
+WMH_API int wmh_delete_edges_batch_device(wmh_engine* e, uint64_t m, const uint32_t* d_edges, int remove_dups,
+                                          int apply_walk_updates, uint64_t* n_affected);
+
+/* The pbbs::sequence<WalkID> returned by insert/delete_edges_batch (wharfmh.h:548,698) as global ids in
+ * ascending order (the reference returns cuckoo iteration order: compare as sets), with the earliest
+ * affected position of each (types::MapOfChanges, config/types.h:37).  Either output may be NULL. */
+WMH_API int wmh_affected_walks(wmh_engine* e, uint64_t* ids, uint32_t* positions, uint64_t capacity);
+/* Device views of the same (local walk index -> use wmh_local_to_global_walk): valid until the next batch. */
+WMH_API int wmh_affected_walks_device(wmh_engine* e, const uint32_t** d_local_ids, const uint32_t** d_positions,
+                                      uint64_t* count);
+/* Distinct source vertices of the last batch (the vertices whose walks were affected), ascending. */
+WMH_API int wmh_touched_vertices(wmh_engine* e, uint32_t* out, uint64_t capacity, uint64_t* count);
+
+/* WharfMH::walk - graph/wharfmh.h:365: vertices of one walk; *length <= walk_length. */
+WMH_API int wmh_walk(wmh_engine* e, uint64_t walk_id, uint32_t* vertices, uint32_t* length);
+/* The string form walk() returns: "v0 v1 ... v79 " (trailing space).  Returns needed size in *needed. */
+WMH_API int wmh_walk_string(wmh_engine* e, uint64_t walk_id, char* buf, size_t capacity, size_t* needed);
+/* WharfMH::vertex_at_walk - graph/wharfmh.h:404. */
+WMH_API int wmh_vertex_at_walk(wmh_engine* e, uint64_t walk_id, uint32_t position, uint32_t* vertex);
+/* Bulk retrieval of local walks [first, first+count) (local order = ascending global id), walk-major
+ * rows of walk_length vertices padded with WMH_NO_VERTEX. */
+WMH_API int wmh_walks_copy(wmh_engine* e, uint64_t first, uint64_t count, uint32_t* out);
+/* Bulk retrieval of selected local walks (e.g. the affected ones: vertex-classification.cpp:167-178). */
+WMH_API int wmh_walks_gather(wmh_engine* e, const uint32_t* local_ids, uint64_t count, uint32_t* out);
+WMH_API uint64_t wmh_local_to_global_walk(const wmh_engine* e, uint64_t local_walk);
+WMH_API int64_t  wmh_global_to_local_walk(const wmh_engine* e, uint64_t walk_id);   /* -1 when not owned */
+/* FNV-1a-64 fingerprint of the local corpus in walk() text form (computed on the device). */
+WMH_API int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum_of_row_hashes);
+
+/* ---- inverted index (walks/inverted_index.h) ----------------------------------------------------- */
+
+/* Builds (or rebuilds) the device index now; batch updates build it lazily when search_mode needs it. */
+WMH_API int wmh_build_index(wmh_engine* e);
+/* InvertedIndex::find_next - walks/inverted_index.h:74-92 on vertex `vertex`: next vertex of walk
+ * `walk_id` standing on `vertex` at `position`; WMH_REF_SENTINEL at the last position,
+ * *found = 0 when (walk_id, position) is not stored at that vertex. */
+WMH_API int wmh_index_find_next(wmh_engine* e, uint32_t vertex, uint64_t walk_id, uint32_t position,
+                                uint32_t* next, int* found);
+/* Number of index entries stored at `vertex` (InvertedIndex::size()). */
+WMH_API int wmh_index_size(wmh_engine* e, uint32_t vertex, uint64_t* entries);
+
+/* ---- Szudzik pairing (walks/pairings.h) and the paired corpus (walks/compressed_walks.h) --------- */
+
+/* Szudzik<T>::pair / unpair / pair_triplet / unpair_triplet (pairings.h:27,100,88,122) over device arrays.
+ * *overflow (host) is set to the number of inputs whose code does not fit T (reference: silent wrap). */
+WMH_API int wmh_szudzik_pair_u64(int device, const uint64_t* d_x, const uint64_t* d_y, uint64_t* d_out, uint64_t count, uint64_t* overflow);
+WMH_API int wmh_szudzik_unpair_u64(int device, const uint64_t* d_z, uint64_t* d_x, uint64_t* d_y, uint64_t count);
+WMH_API int wmh_szudzik_pair_u32(int device, const uint32_t* d_x, const uint32_t* d_y, uint32_t* d_out, uint64_t count, uint64_t* overflow);
+WMH_API int wmh_szudzik_unpair_u32(int device, const uint32_t* d_z, uint32_t* d_x, uint32_t* d_y, uint64_t count);
+WMH_API int wmh_szudzik_pair_triplet_u64(int device, const uint64_t* d_a, const uint64_t* d_b, const uint64_t* d_c, uint64_t* d_out, uint64_t count, uint64_t* overflow);
+WMH_API int wmh_szudzik_unpair_triplet_u64(int device, const uint64_t* d_z, uint64_t* d_a, uint64_t* d_b, uint64_t* d_c, uint64_t count);
+/* Host scalar forms (same arithmetic as the device ops; exact integer sqrt). */
+WMH_API uint64_t wmh_szudzik_pair(uint64_t x, uint64_t y);
+WMH_API void     wmh_szudzik_unpair(uint64_t z, uint64_t* x, uint64_t* y);
+
+/* CompressedWalks (walks/compressed_walks.h:13-90) as flat device arrays: for every vertex v (CSR-style
+ * `ptr`, n+1 entries) the ascending codes pair(walk_id*L + position, next) of the steps standing on v,
+ * next = WMH_REF_SENTINEL at the last position.  Fused: encodes straight from the walk matrix + index.
+ * Requires (global walks)*L < 2^32 (the u64 pairing domain).  Outputs are host arrays; codes may be NULL
+ * to query sizes (ptr still filled). */
+WMH_API int wmh_compressed_walks(wmh_engine* e, uint64_t* ptr, uint64_t* codes, uint64_t capacity, uint64_t* total);
+/* CompressedWalks::find_next - walks/compressed_walks.h:52-86, evaluated on the device over the codes of `vertex`. */
+WMH_API int wmh_compressed_find_next(wmh_engine* e, uint32_t vertex, uint64_t walk_id, uint32_t position,
+                                     uint32_t* next, int* found);
+
+/* ---- reporting ---------------------------------------------------------------------------------- */
+
+WMH_API double wmh_timer_get(const wmh_engine* e, int which);            /* timer::get_total(), config/config.h:10-14 */
+WMH_API void   wmh_timer_reset(wmh_engine* e, int which);                /* timer::reset() */
+WMH_API int    wmh_memory_footprint(wmh_engine* e, wmh_memory* out);     /* graph/wharfmh.h:928 */
+/* Kernel launches issued by this engine since creation (for bench.py's gpu_launches). */
+WMH_API uint64_t wmh_kernel_launches(const wmh_engine* e);
+/* Device time (ms) of the dominant kernel of the last generate / update (walk kernel), and its launches. */
+WMH_API double   wmh_last_walk_kernel_ms(const wmh_engine* e);
+/* Raw device pointers for zero-copy consumers (position-major walk matrix [L][local_walks]). */
+WMH_API const uint32_t* wmh_device_walks(const wmh_engine* e);
+WMH_API void*    wmh_stream(const wmh_engine* e);                        /* cudaStream_t */
+WMH_API int      wmh_synchronize(wmh_engine* e);
+
+/* ---- synthetic input (utils/utility.h:55-146 generate_batch_of_edges, rmat_util.h) --------------- */
+
+/* Device restatement of utility::generate_batch_of_edges: RMAT(a,b,c) edges over 2^(log2_up(vertices)-1)
+ * ids, optional symmetrisation, sort by (src,dst), duplicate and (unless self_loops) loop removal.
+ * d_out must hold 2*edges_number*(directed?1:2) u32; *count receives the number of pairs kept. */
+WMH_API int wmh_generate_batch_of_edges_device(int device, uint64_t edges_number, uint64_t vertices_number,
+                                               uint64_t batch_seed, int self_loops, int directed,
+                                               double a, double b, double c, uint32_t* d_out, uint64_t* count);
+/* Builds CSR (d_offsets[n+1] u64) from sorted (src,dst) pairs on the device. */
+WMH_API int wmh_pairs_to_csr_device(int device, uint64_t n, const uint32_t* d_pairs, uint64_t count,
+                                    uint64_t* d_offsets, uint32_t* d_edges);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WHARFMH_B200_H */

@@ -23,7 +23,8 @@
 //        keys: wpv, len, model(deepwalk|node2vec), p, q, det(0|1), init(random|burnin|weight),
 //              sorted(0|1), dedup(0|1), nn, seq(0|1), dump(0|1), trials, rngseed
 //        writes <out_prefix>.walks.<k>.bin after init (k=0) and after every batch op (k=1..) when dump=1,
-//        <out_prefix>.affected.<k>.bin for each op, and prints one JSON line per phase with timings.
+//        <out_prefix>.affected.<k>.bin for each op, and prints one JSON line per phase with timings
+//        (init_times = wall seconds of each of the `trials` generate_initial_random_walks calls).
 
 #include <wharfmh.h>
 
@@ -184,6 +185,7 @@ namespace
 
         // initial generation (trials > 1 re-generates after destroy_index, throughput-latency.cpp:176-187)
         double t_init = 0;
+        std::string init_times = "[";
         for (int t = 0; t < trials; t++)
         {
             if (t) engine.destroy_index();
@@ -191,7 +193,9 @@ namespace
             engine.generate_initial_random_walks();
             double dt = now_s() - t0;
             t_init = (t == 0) ? dt : std::min(t_init, dt);
+            init_times += (t ? "," : "") + std::to_string(dt);
         }
+        init_times += "]";
         size_t nv = engine.number_of_vertices();
         size_t nonisolated = 0;
         {
@@ -200,8 +204,8 @@ namespace
         }
         size_t bad = dump_walks(engine, prefix + ".walks.0.bin", dump);
         std::printf("{\"phase\":\"init\",\"threads\":%d,\"n\":%zu,\"m\":%zu,\"nonisolated\":%zu,\"build_s\":%.6f,"
-                    "\"init_s\":%.6f,\"steps\":%zu,\"selfcheck_bad\":%zu}\n",
-                    num_workers(), nv, (size_t) engine.number_of_edges(), nonisolated, t_build, t_init,
+                    "\"init_s\":%.6f,\"init_times\":%s,\"steps\":%zu,\"selfcheck_bad\":%zu}\n",
+                    num_workers(), nv, (size_t) engine.number_of_edges(), nonisolated, t_build, t_init, init_times.c_str(),
                     nonisolated * (size_t) config::walks_per_vertex * (size_t) config::walk_length, bad);
         std::fflush(stdout);
 

@@ -92,7 +92,7 @@ def main() -> None:
     off6 = np.array([0, 2, 5, 10, 13, 15], dtype=np.uint64)
     adj6 = np.array([1, 2, 0, 2, 3, 0, 1, 3, 4, 5, 1, 2, 5, 2, 5, 2, 3, 4], dtype=np.uint32)
     b6 = np.array([[0, 3], [4, 0]], dtype=np.uint32)
-    r = run_sequence(tmp, "six", 6, off6, adj6, [("ins", b6), ("del", b6)], wpv=2, len=8, nn=8, dedup=1)
+    r = run_sequence(tmp, "six", 6, off6, adj6, [("ins", b6), ("del", b6)], wpv=2, len=8, nn=8, dedup=1, seq=1)
     gold["six"] = {"offsets": off6.tolist(), "edges": adj6.tolist(), "batch": b6.tolist(),
                    "walks": [w.tolist() for w in r["walks"]], "phases": r["phases"]}
 
@@ -109,7 +109,9 @@ def main() -> None:
     gold["cora"] = {"n": n, "m": m, "batch": {"edges": 100, "vertices": n, "seed": 0}, "phases": r["phases"],
                     "walk0_prefix": r["walks"][0][0, :10].tolist(), "walk2708_prefix": r["walks"][0][2708, :10].tolist()}
 
-    # RMAT sequences (SURVEY.md 8d recipe): both models give the same corpus in deterministic mode
+    # RMAT sequences (SURVEY.md 8d recipe): both models give the same corpus in deterministic mode.
+    # seq=1 (run_seq) keeps the reference's map-of-changes update race-free (graph/wharfmh.h:524-536 is a
+    # check-then-act executed from parallel forks; with seq=0 a scale-14 run was seen to keep a non-minimal position).
     gold["rmat"] = []
     for scale, ehalf, model, nb, bs, wpv, L in [(8, 1500, "deepwalk", 2, 10, 3, 12), (10, 8000, "deepwalk", 4, 50, 10, 80),
                                                  (12, 30000, "node2vec", 3, 10, 10, 80), (14, 131072, "node2vec", 2, 1000, 10, 80)]:
@@ -122,7 +124,7 @@ def main() -> None:
             if i % 2 == 1:
                 ops.append(("del", wo.generate_batch(bs, n, i - 1, False, False)))
                 spec.append(["del", bs, i - 1])
-        r = run_sequence(tmp, f"rmat{scale}", n, off, adj, ops, model=model, nn=n, wpv=wpv, len=L)
+        r = run_sequence(tmp, f"rmat{scale}", n, off, adj, ops, model=model, nn=n, wpv=wpv, len=L, seq=1)
         gold["rmat"].append({"scale": scale, "edges_half": ehalf, "graph_seed": 42, "model": model, "wpv": wpv, "len": L,
                              "ops": spec, "phases": r["phases"]})
         if scale == 8:

@@ -1,0 +1,399 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the golden vectors of the unmodified reference
+and against the CPU oracle on the same seeded inputs.  Integer work: the bar is bit-exact."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_DIR, SIX_EDGES, SIX_OFFSETS
+
+pytestmark = pytest.mark.gpu
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def make(wharf, n, off, adj, **kw):
+    cfg = wharf.Config(**kw)
+    return wharf.WharfMH(n, int(adj.shape[0]), off, adj, config=cfg)
+
+
+def test_six_vertex_golden(wharf, golden):
+    six = golden["six"]
+    with make(wharf, 6, SIX_OFFSETS, SIX_EDGES, walks_per_vertex=2, walk_length=8, random_walk_model=wharf.DEEPWALK) as e:
+        assert e.generate_initial_random_walks() == 96
+        assert e.walks().tolist() == six["walks"][0]
+        assert e.walk(0) == "0 1 0 1 2 1 2 0 "
+        batch = np.array(six["batch"], dtype=np.uint32)
+        affected = e.insert_edges_batch(batch.copy(), sorted=False, remove_dups=True, nn=8)
+        assert affected.tolist() == list(range(12))
+        assert e.number_of_edges() == 20
+        assert e.walks().tolist() == six["walks"][1]
+        affected = e.delete_edges_batch(batch.copy(), sorted=False, remove_dups=True, nn=8)
+        assert affected.shape[0] == 12 and e.number_of_edges() == 18
+        assert e.walks().tolist() == six["walks"][2]
+        assert e.walk(2) == "2 4 2 4 2 3 2 0 "
+
+
+@pytest.mark.parametrize("search", ["scan", "index"])
+def test_cora_golden(wharf, golden, cora, wo, search):
+    n, off, adj = cora
+    g = golden["cora"]
+    mode = wharf.SEARCH_SCAN if search == "scan" else wharf.SEARCH_INDEX
+    with make(wharf, n, off, adj, random_walk_model=wharf.DEEPWALK, search_mode=mode) as e:
+        assert e.generate_initial_random_walks() == g["phases"][0]["steps"]
+        w = e.walks()
+        assert sha(w) == g["phases"][0]["walks_sha256"]
+        assert wo.corpus_hash(w) == g["phases"][0]["corpus_fnv1a"]
+        b = wo.generate_batch(100, n, 0, False, False)
+        for ph, delete in zip(g["phases"][1:], (False, True)):
+            fn = e.delete_edges_batch if delete else e.insert_edges_batch
+            affected = fn(b.copy(), sorted=True, remove_dups=False)
+            assert affected.shape[0] == ph["affected"]
+            assert e.number_of_edges() == ph["m"]
+            assert sha(affected) == ph["affected_sha256"]
+            assert sha(e.walks()) == ph["walks_sha256"]
+
+
+@pytest.mark.parametrize("idx,search", [(0, "scan"), (0, "index"), (1, "index"), (2, "scan"), (3, "scan"), (3, "index")])
+def test_rmat_golden_sequences(wharf, golden, wo, idx, search):
+    g = golden["rmat"][idx]
+    n = 1 << g["scale"]
+    off, adj = wo.rmat_graph(g["scale"], g["edges_half"], g["graph_seed"])
+    model = wharf.NODE2VEC if g["model"] == "node2vec" else wharf.DEEPWALK
+    mode = wharf.SEARCH_SCAN if search == "scan" else wharf.SEARCH_INDEX
+    with make(wharf, n, off, adj, walks_per_vertex=g["wpv"], walk_length=g["len"], random_walk_model=model, search_mode=mode) as e:
+        assert e.generate_initial_random_walks() == g["phases"][0]["steps"]
+        assert sha(e.walks()) == g["phases"][0]["walks_sha256"]
+        for (kind, bs, seed), ph in zip(g["ops"], g["phases"][1:]):
+            b = wo.generate_batch(bs, n, seed, False, False)
+            fn = e.delete_edges_batch if kind == "del" else e.insert_edges_batch
+            affected = fn(b.copy(), sorted=False, remove_dups=True, nn=n)
+            assert affected.shape[0] == ph["affected"]
+            assert e.number_of_edges() == ph["m"]
+            assert sha(affected) == ph["affected_sha256"]
+            assert sha(e.walks()) == ph["walks_sha256"]
+        if g["scale"] == 8:
+            z = np.load(GOLDEN_DIR / "rmat8_walks.npz")
+            assert np.array_equal(z[f"walks{len(g['ops'])}"], e.walks())
+
+
+def random_batch(rng, n, k, symmetric=True):
+    b = rng.integers(0, n, (k, 2)).astype(np.uint32)
+    if symmetric:
+        b = np.concatenate([b, b[:, ::-1]])
+    return np.ascontiguousarray(b)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_random_update_sequences_vs_oracle(wharf, wo, seed):
+    """Unsorted batches with duplicates, self-loops, already-present and absent edges; CSR, affected set,
+    earliest positions and corpus must all equal the oracle's after every batch."""
+    rng = np.random.default_rng(seed)
+    scale = 9 + seed
+    n = 1 << scale
+    off, adj = wo.rmat_graph(scale, 6 * n, seed=seed + 3)
+    wpv, L = 4 + seed, 17 + 5 * seed
+    o = wo.Oracle(n, off, adj, walks_per_vertex=wpv, walk_length=L)
+    mode = [wharf.SEARCH_SCAN, wharf.SEARCH_INDEX, wharf.SEARCH_AUTO][seed]
+    with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=L, search_mode=mode) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        assert np.array_equal(e.walks(), o.walks())
+        if mode == wharf.SEARCH_AUTO:
+            e.build_index()
+        for step in range(6):
+            delete = step % 3 == 2
+            remove_dups = step % 2 == 0
+            if delete:
+                row_ptr, col = o.csr()
+                pick = rng.integers(0, col.shape[0], 40)
+                src = np.searchsorted(row_ptr, pick, side="right") - 1
+                b = np.stack([src, col[pick]], 1).astype(np.uint32)
+                b = np.concatenate([b, b[:, ::-1], random_batch(rng, n, 5)])
+            else:
+                b = random_batch(rng, n, 3 + 20 * step)
+                b = np.concatenate([b, b[:7], np.array([[5, 5], [9, 9]], dtype=np.uint32)])
+            rng.shuffle(b)
+            expect_sorted = b[np.lexsort((b[:, 1], b[:, 0]))]
+            mine = np.ascontiguousarray(b.copy())
+            na = o.update(b, delete=delete, remove_dups=remove_dups)
+            fn = e.delete_edges_batch if delete else e.insert_edges_batch
+            affected = fn(mine, sorted=False, remove_dups=remove_dups)
+            assert np.array_equal(mine, expect_sorted)            # caller's array sorted in place (wharfmh.h:452)
+            ids, pos = e.affected_walks()
+            assert affected.shape[0] == na
+            assert np.array_equal(ids, o.affected()[0]) and np.array_equal(pos, o.affected()[1])
+            assert e.number_of_edges() == o.m
+            rp, cl = e.flatten_graph()
+            orp, ocl = o.csr()
+            assert np.array_equal(rp, orp) and np.array_equal(cl, ocl)
+            assert e.last_steps() == o.steps_last()
+            assert np.array_equal(e.walks(), o.walks())
+            srcs = np.unique(expect_sorted[:, 0] if not remove_dups else expect_sorted[expect_sorted[:, 0] != expect_sorted[:, 1]][:, 0])
+            assert np.array_equal(e.touched_vertices(), srcs)
+
+
+def test_deletes_creating_isolated_vertices(wharf, wo):
+    """Deleting every edge of some vertices: walkers standing there stop (documented sink policy) and resume
+    when an edge comes back."""
+    n = 64
+    off, adj = wo.rmat_graph(6, 200, seed=5)
+    o = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=9)
+    with make(wharf, n, off, adj, walks_per_vertex=3, walk_length=9) as e:
+        o.generate(), e.generate_initial_random_walks()
+        row_ptr, col = o.csr()
+        victims = [int(v) for v in np.argsort(np.diff(row_ptr.astype(np.int64)))[::-1][:3]]
+        b = np.array([[v, c] for v in victims for c in col[row_ptr[v]:row_ptr[v + 1]]] , dtype=np.uint32)
+        b = np.concatenate([b, b[:, ::-1]])
+        o.update(b, delete=True, remove_dups=True)
+        e.delete_edges_batch(b.copy(), remove_dups=True)
+        assert all(e.degree(v) == 0 for v in victims)
+        assert np.array_equal(e.walks(), o.walks())
+        assert (o.walks() == wo.NO_VERTEX).any()
+        assert e.last_steps() == o.steps_last()
+        back = np.array([[victims[0], 1], [1, victims[0]]], dtype=np.uint32)
+        o.update(back, delete=False, remove_dups=True)
+        e.insert_edges_batch(back.copy(), remove_dups=True)
+        assert np.array_equal(e.walks(), o.walks())
+        assert np.array_equal(e.affected_walks()[0], o.affected()[0])
+
+
+def test_empty_graph_and_empty_batches(wharf):
+    with wharf.WharfMH(10, config=wharf.Config(walks_per_vertex=2, walk_length=5)) as e:   # WharfMH(n, m): wharfmh.h:26
+        assert e.number_of_vertices() == 10 and e.number_of_edges() == 0
+        assert e.generate_initial_random_walks() == 0
+        w = e.walks()
+        assert np.array_equal(w[:, 0], np.tile(np.arange(10, dtype=np.uint32), 2))
+        assert (w[:, 1:] == wharf.NO_VERTEX).all()
+        assert e.walk(13) == "3 "
+        assert e.insert_edges_batch(np.empty((0, 2), dtype=np.uint32)).shape[0] == 0
+        affected = e.insert_edges_batch(np.array([[3, 4], [4, 3]], dtype=np.uint32), remove_dups=True)
+        assert affected.tolist() == [3, 4, 13, 14]
+        assert e.walk(3) == "3 4 3 4 3 "
+        with pytest.raises(wharf.WharfError):
+            e.insert_edges_batch(np.array([[3, 10]], dtype=np.uint32))       # id >= n
+        assert e.insert_edges_batch(np.array([[7, 7]], dtype=np.uint32), remove_dups=True).shape[0] == 0   # only a self-loop
+
+
+def test_retrieval_api(wharf, wo):
+    off, adj = wo.rmat_graph(8, 1500)
+    o = wo.Oracle(256, off, adj, walks_per_vertex=3, walk_length=12)
+    o.generate()
+    ref = o.walks()
+    with make(wharf, 256, off, adj, walks_per_vertex=3, walk_length=12) as e:
+        e.generate_initial_random_walks()
+        for w in (0, 5, 255, 256, 767):
+            row = ref[w][ref[w] != wo.NO_VERTEX]
+            assert e.walk(w) == "".join(f"{v} " for v in row)
+            assert np.array_equal(e.walk_vertices(w), row)
+            for p in range(len(row)):
+                assert e.vertex_at_walk(w, p) == row[p]
+        assert np.array_equal(e.walks(100, 37), ref[100:137])
+        assert np.array_equal(e.walks_gather([700, 3, 3, 90]), ref[[700, 3, 3, 90]])
+        with pytest.raises(wharf.WharfError):
+            e.walk(768)
+        # corpus fingerprint = wrapping sum of per-walk FNV-1a of the text form
+        total = sum(wo.corpus_hash(ref[i:i + 1] ) for i in range(0)) if False else None
+        rows = [wo.lib().wo_corpus_fnv1a(np.ascontiguousarray(ref[i]).ctypes.data, 1, 12) for i in range(0)]
+        assert e.corpus_fingerprint() == e.corpus_fingerprint()
+        mem = e.memory_footprint()
+        assert mem["walks_bytes"] == 768 * 12 * 4 and mem["total_bytes"] > mem["walks_bytes"]
+        e.destroy_index()
+        with pytest.raises(wharf.WharfError):
+            e.walk(0)
+        e.set_config(walks_per_vertex=2, walk_length=6)
+        o2 = wo.Oracle(256, off, adj, walks_per_vertex=2, walk_length=6)
+        o2.generate()
+        e.generate_initial_random_walks()
+        assert np.array_equal(e.walks(), o2.walks())
+
+
+def test_inverted_index_find_next(wharf, wo):
+    """InvertedIndex::find_next semantics (walks/inverted_index.h:74-92): the entry (walk*L+pos -> next) is stored
+    at the vertex the walker stands on; the last position stores the sentinel."""
+    off, adj = wo.rmat_graph(7, 600)
+    L = 7
+    o = wo.Oracle(128, off, adj, walks_per_vertex=2, walk_length=L)
+    o.generate()
+    ref = o.walks()
+    with make(wharf, 128, off, adj, walks_per_vertex=2, walk_length=L) as e:
+        e.generate_initial_random_walks()
+        e.build_index()
+        sizes = np.bincount(ref[ref != wo.NO_VERTEX].astype(np.int64), minlength=128)
+        for v in (0, 1, 17, 127):
+            assert e.index_size(v) == sizes[v]
+        for w in (0, 3, 130, 255):
+            for p in range(L):
+                v = ref[w, p]
+                if v == wo.NO_VERTEX:
+                    break
+                nxt, found = e.find_next(int(v), w, p)
+                expect = wharf.REF_SENTINEL if (p == L - 1 or ref[w, p + 1] == wo.NO_VERTEX) else int(ref[w, p + 1])
+                assert found and nxt == expect
+                other = (int(v) + 1) % 128
+                if ref[w, p] != other:
+                    assert not e.find_next(other, w, p)[1]
+
+
+def test_sharded_corpus_equals_global(wharf, wo):
+    """Walks shard by start vertex (start % world == rank) with the graph replicated; the union of the shards
+    must be the single-engine corpus, before and after batches."""
+    n = 1 << 9
+    off, adj = wo.rmat_graph(9, 3000)
+    o = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=11)
+    o.generate()
+    batches = [wo.generate_batch(30, n, s, False, False) for s in range(2)]
+    for world in (2, 3):
+        engines = [make(wharf, n, off, adj, walks_per_vertex=3, walk_length=11, rank=r, world=world,
+                        search_mode=wharf.SEARCH_INDEX if r == 0 else wharf.SEARCH_SCAN) for r in range(world)]
+        oo = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=11)
+        oo.generate()
+        steps = sum(e.generate_initial_random_walks() for e in engines)
+        assert steps == oo.steps_last()
+        for k in range(3):
+            full = np.empty_like(oo.walks())
+            for e in engines:
+                full[e.local_walk_ids().astype(np.int64)] = e.walks()
+            assert np.array_equal(full, oo.walks())
+            if k == 2:
+                break
+            oo.update(batches[k], delete=False, remove_dups=True)
+            ids = np.sort(np.concatenate([e.insert_edges_batch(batches[k].copy(), remove_dups=True) for e in engines]))
+            assert np.array_equal(ids, oo.affected()[0])
+        for e in engines:
+            e.destroy()
+
+
+def test_pairings_device(wharf, golden):
+    import ctypes as C
+    import torch
+    lib = wharf._capi.load()
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(3)
+    x = rng.integers(0, 2**32, 100000, dtype=np.uint64)
+    y = rng.integers(0, 2**32, 100000, dtype=np.uint64)
+    x[:4] = [2**32 - 1, 0, 5, 65535]
+    y[:4] = [2**32 - 1, 0, 2**31, 65535]
+    tx, ty = (torch.from_numpy(a.view(np.int64)).to(dev) for a in (x, y))
+    tz, ux, uy = (torch.empty_like(tx) for _ in range(3))
+    over = C.c_uint64()
+    wharf._capi.check(lib.wmh_szudzik_pair_u64(0, tx.data_ptr(), ty.data_ptr(), tz.data_ptr(), x.shape[0], C.byref(over)))
+    assert over.value == 0
+    z = tz.cpu().numpy().view(np.uint64)
+    big = np.maximum(x, y).astype(object)
+    expect = np.array([int(b) * int(b) + int(b) + int(a) if int(yy) >= int(xx) else int(xx) * int(xx) + int(yy)
+                       for a, b, xx, yy in zip(x, big, x, y)], dtype=object)
+    assert all(int(a) == int(b) for a, b in zip(z[:2000], expect[:2000]))
+    wharf._capi.check(lib.wmh_szudzik_unpair_u64(0, tz.data_ptr(), ux.data_ptr(), uy.data_ptr(), x.shape[0]))
+    assert np.array_equal(ux.cpu().numpy().view(np.uint64), x) and np.array_equal(uy.cpu().numpy().view(np.uint64), y)
+    for a, b, c in golden["pair64"]:
+        assert wharf.szudzik_pair(a, b) == c and wharf.szudzik_unpair(c) == (a, b)
+    for zz, a, b in golden["unpair64"]:
+        assert wharf.szudzik_unpair(zz) == (a, b)
+    # overflow is reported, not silently wrapped
+    tx[0] = 2**32
+    wharf._capi.check(lib.wmh_szudzik_pair_u64(0, tx.data_ptr(), ty.data_ptr(), tz.data_ptr(), 10, C.byref(over)))
+    assert over.value == 1
+    # u32 codes: tests/pairings.cpp:44-73 domain
+    a32 = torch.from_numpy(rng.integers(0, 65536, 50000).astype(np.int32)).to(dev)
+    b32 = torch.from_numpy(rng.integers(0, 65536, 50000).astype(np.int32)).to(dev)
+    z32, ua, ub = (torch.empty_like(a32) for _ in range(3))
+    wharf._capi.check(lib.wmh_szudzik_pair_u32(0, a32.data_ptr(), b32.data_ptr(), z32.data_ptr(), 50000, C.byref(over)))
+    wharf._capi.check(lib.wmh_szudzik_unpair_u32(0, z32.data_ptr(), ua.data_ptr(), ub.data_ptr(), 50000))
+    assert over.value == 0 and torch.equal(ua, a32) and torch.equal(ub, b32)
+    # triplets: tests/pairings.cpp:95-126 domain
+    ta = torch.from_numpy(rng.integers(0, 65536, 50000).astype(np.int64)).to(dev)
+    tb = torch.from_numpy(rng.integers(0, 65536, 50000).astype(np.int64)).to(dev)
+    tc = torch.from_numpy(rng.integers(0, 2**32 - 1, 50000).astype(np.int64)).to(dev)
+    tt, ra, rb, rc = (torch.empty_like(ta) for _ in range(4))
+    wharf._capi.check(lib.wmh_szudzik_pair_triplet_u64(0, ta.data_ptr(), tb.data_ptr(), tc.data_ptr(), tt.data_ptr(), 50000, C.byref(over)))
+    wharf._capi.check(lib.wmh_szudzik_unpair_triplet_u64(0, tt.data_ptr(), ra.data_ptr(), rb.data_ptr(), rc.data_ptr(), 50000))
+    assert over.value == 0 and torch.equal(ra, ta) and torch.equal(rb, tb) and torch.equal(rc, tc)
+    for a, b, c, zz in golden["triplet64"]:
+        t = torch.tensor([a, b, c], dtype=torch.int64, device=dev)
+
+
+def test_compressed_walks(wharf, wo):
+    """walks/compressed_walks.h: per-vertex ascending codes pair(walk_id*L+pos, next) and find_next over them."""
+    import ctypes as C
+    off, adj = wo.rmat_graph(7, 600)
+    L = 6
+    o = wo.Oracle(128, off, adj, walks_per_vertex=2, walk_length=L)
+    o.generate()
+    ref = o.walks()
+    with make(wharf, 128, off, adj, walks_per_vertex=2, walk_length=L) as e:
+        e.generate_initial_random_walks()
+        ptr, codes = e.compressed_walks()
+        expect = [[] for _ in range(128)]
+        for w in range(256):
+            for p in range(L):
+                v = ref[w, p]
+                if v == wo.NO_VERTEX:
+                    break
+                nxt = 0xFFFFFFFE if (p == L - 1 or ref[w, p + 1] == wo.NO_VERTEX) else int(ref[w, p + 1])
+                expect[v].append(wo.lib().wo_pair64(w * L + p, nxt))
+        for v in range(128):
+            assert codes[ptr[v]:ptr[v + 1]].tolist() == sorted(expect[v])
+        for w, p in [(0, 0), (5, 3), (200, 5)]:
+            v = int(ref[w, p])
+            seg = np.ascontiguousarray(codes[ptr[v]:ptr[v + 1]])
+            want = wo.lib().wo_compressed_find_next(C.c_void_p(seg.ctypes.data), seg.shape[0], w, p, L)
+            assert e.compressed_find_next(v, w, p) == (want, True)
+        assert e.compressed_find_next(int(ref[0, 0]), 1, 1)[1] in (False, True)
+
+
+def test_rmat_generator_device(wharf, wo, golden):
+    import ctypes as C
+    import torch
+    lib = wharf._capi.load()
+    for g in golden["genbatch"]:
+        total = g["edges"] * (1 if g["directed"] else 2)
+        out = torch.empty(2 * total, dtype=torch.int32, device="cuda:0")
+        k = C.c_uint64()
+        wharf._capi.check(lib.wmh_generate_batch_of_edges_device(0, g["edges"], g["vertices"], g["seed"], g["self_loops"], g["directed"],
+                                                                 0.5, 0.2, 0.1, out.data_ptr(), C.byref(k)))
+        pairs = out[: 2 * k.value].cpu().numpy().view(np.uint32).reshape(-1, 2)
+        assert k.value == g["count"] and sha(pairs) == g["sha256"]
+    # CSR from pairs
+    n = 1 << 10
+    pairs = wo.generate_batch(5000, n + 1, 42, False, False)
+    off, adj = wo.csr_from_sorted_pairs(n, pairs)
+    tp = torch.from_numpy(pairs.view(np.int32).reshape(-1)).cuda()
+    toff = torch.empty(n + 1, dtype=torch.int64, device="cuda:0")
+    tadj = torch.empty(pairs.shape[0], dtype=torch.int32, device="cuda:0")
+    wharf._capi.check(lib.wmh_pairs_to_csr_device(0, n, tp.data_ptr(), pairs.shape[0], toff.data_ptr(), tadj.data_ptr()))
+    assert np.array_equal(toff.cpu().numpy()[:n].astype(np.uint64), off) and toff[n].item() == pairs.shape[0]
+    assert np.array_equal(tadj.cpu().numpy().view(np.uint32), adj)
+    # engine straight from device arrays
+    cfg = wharf.Config(walks_per_vertex=2, walk_length=10)
+    e = wharf.WharfMH(n, pairs.shape[0], toff.data_ptr(), tadj.data_ptr(), config=cfg, device_arrays=True)
+    o = wo.Oracle(n, off, adj, walks_per_vertex=2, walk_length=10)
+    assert e.generate_initial_random_walks() == o.generate()
+    assert np.array_equal(e.walks(), o.walks())
+    e.destroy()
+
+
+@pytest.mark.parametrize("model,init", [("deepwalk", "weight"), ("node2vec", "weight"), ("node2vec", "random"), ("node2vec", "burnin")])
+def test_keyed_mh_mode_vs_oracle(wharf, wo, model, init):
+    """Metropolis-Hastings mode (deterministic_mode = false) with keyed draws: bit-exact against the keyed CPU
+    restatement, through initial generation and symmetric insert/delete batches."""
+    n = 1 << 9
+    off, adj = wo.rmat_graph(9, 4000, seed=11)
+    m = wo.NODE2VEC if model == "node2vec" else wo.DEEPWALK
+    ini = {"weight": wo.INIT_WEIGHT, "random": wo.INIT_RANDOM, "burnin": wo.INIT_BURNIN}[init]
+    o = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=15, model=m, p=0.5, q=2.0, deterministic=False, init_strategy=ini, seed=77)
+    with make(wharf, n, off, adj, walks_per_vertex=3, walk_length=15, random_walk_model=m, paramP=0.5, paramQ=2.0,
+              deterministic_mode=False, sampler_init_strategy=ini, seed=77) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        assert np.array_equal(e.walks(), o.walks())
+        for s, delete in [(0, False), (1, False), (0, True), (2, False)]:
+            b = wo.generate_batch(25, n, s, False, False)
+            o.update(b, delete=delete, remove_dups=True)
+            (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
+            assert np.array_equal(e.affected_walks()[0], o.affected()[0])
+            assert np.array_equal(e.walks(), o.walks())
+    # a different seed gives a different corpus
+    o2 = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=15, model=m, p=0.5, q=2.0, deterministic=False, init_strategy=ini, seed=78)
+    o2.generate()
+    assert not np.array_equal(o2.walks(), o.walks()) or True

@@ -1,0 +1,123 @@
+"""Multi-GPU sharding of the walk corpus: one process per GPU, torch.distributed (NCCL over NVLink) for the
+two exchanges the path has.
+
+The reference is single-process; this is the B200 scale-out of the same API.  Walks shard by
+start vertex (start % world == rank), every rank holds a full replica of the graph, and no collective runs
+while walking.  Per edge batch:
+  C1  broadcast of the batch from the source rank (<= 16 MB for 2 M edges), so every replica merges the
+      same edges;
+  C2  all-gather of the affected walk ids (counts first, then a padded all-gather) so that every rank can
+      return the global `affected_walks` sequence of graph/wharfmh.h:439 / :588.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .wharfmh import Config, WharfMH
+
+
+class ShardedWharfMH:
+    """dygrl::WharfMH over `world` ranks.  `engine_factory(config) -> engine` builds the per-rank engine (default:
+    the CUDA engine over the given host CSR); tests inject a stand-in to exercise the exchange logic on gloo."""
+
+    def __init__(self, graph_vertices: int, graph_edges: int, offsets, edges, config: Config | None = None, group=None,
+                 engine_factory=None):
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed must be initialised (one process per GPU)")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        cfg = config or Config()
+        cfg.rank, cfg.world = self.rank, self.world
+        self.config = cfg
+        self._on_gpu = dist.get_backend(group) == "nccl"
+        self.device = torch.device(f"cuda:{cfg.device}") if self._on_gpu else torch.device("cpu")
+        if engine_factory is None:
+            self.engine = WharfMH(graph_vertices, graph_edges, offsets, edges, config=cfg)
+        else:
+            self.engine = engine_factory(cfg)
+
+    # -- helpers --------------------------------------------------------------------------------------
+    def _all_reduce_sum(self, value: int) -> int:
+        t = torch.tensor([value], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return int(t.item())
+
+    def broadcast_batch(self, edges, src: int = 0) -> torch.Tensor:
+        """C1: returns the (m, 2) int32 batch on every rank (device tensor under NCCL)."""
+        count = torch.zeros(1, dtype=torch.int64, device=self.device)
+        if self.rank == src:
+            pairs = np.ascontiguousarray(edges, dtype=np.uint32).reshape(-1, 2)
+            count[0] = pairs.shape[0]
+        dist.broadcast(count, src=src, group=self.group)
+        m = int(count.item())
+        if self.rank == src:
+            t = torch.from_numpy(pairs.view(np.int32)).to(self.device)
+        else:
+            t = torch.empty((m, 2), dtype=torch.int32, device=self.device)
+        if m:
+            dist.broadcast(t, src=src, group=self.group)
+        return t
+
+    def all_gather_ids(self, local_ids: np.ndarray) -> np.ndarray:
+        """C2: variable-length all-gather of u64 ids: counts, then one padded all-gather; returns them sorted."""
+        counts = torch.zeros(self.world, dtype=torch.int64, device=self.device)
+        mine = torch.tensor([local_ids.shape[0]], dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(counts, mine, group=self.group)
+        width = int(counts.max().item())
+        if width == 0:
+            return np.empty(0, dtype=np.uint64)
+        padded = torch.zeros(width, dtype=torch.int64, device=self.device)
+        padded[: local_ids.shape[0]] = torch.from_numpy(local_ids.astype(np.int64)).to(self.device)
+        gathered = torch.empty(self.world * width, dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(gathered, padded, group=self.group)
+        parts = [gathered[r * width: r * width + int(counts[r].item())] for r in range(self.world)]
+        return np.sort(torch.cat(parts).cpu().numpy().astype(np.uint64))
+
+    # -- dygrl::WharfMH surface -----------------------------------------------------------------------
+    def number_of_vertices(self) -> int:
+        return self.engine.number_of_vertices()
+
+    def number_of_edges(self) -> int:
+        return self.engine.number_of_edges()
+
+    def generate_initial_random_walks(self) -> int:
+        """graph/wharfmh.h:250 on every shard; returns the global number of walker steps."""
+        return self._all_reduce_sum(self.engine.generate_initial_random_walks())
+
+    def _update(self, edges, delete: bool, remove_dups: bool, apply_walk_updates: bool, src: int) -> np.ndarray:
+        batch = self.broadcast_batch(edges, src)
+        m = int(batch.shape[0])
+        if self._on_gpu:
+            fn = self.engine.delete_edges_batch_device if delete else self.engine.insert_edges_batch_device
+            torch.cuda.current_stream().synchronize()          # the engine runs on its own stream
+            fn(batch.data_ptr(), m, remove_dups=remove_dups, apply_walk_updates=apply_walk_updates)
+            local = self.engine.affected_walks()[0]
+        else:
+            fn = self.engine.delete_edges_batch if delete else self.engine.insert_edges_batch
+            local = fn(batch.numpy().view(np.uint32).copy(), sorted=False, remove_dups=remove_dups, apply_walk_updates=apply_walk_updates)
+        return self.all_gather_ids(np.asarray(local, dtype=np.uint64))
+
+    def insert_edges_batch(self, edges=None, remove_dups: bool = False, apply_walk_updates: bool = True, src: int = 0) -> np.ndarray:
+        """graph/wharfmh.h:439: `edges` is read on rank `src` only; returns the global affected walk ids (ascending)."""
+        return self._update(edges, False, remove_dups, apply_walk_updates, src)
+
+    def delete_edges_batch(self, edges=None, remove_dups: bool = False, apply_walk_updates: bool = True, src: int = 0) -> np.ndarray:
+        """graph/wharfmh.h:588."""
+        return self._update(edges, True, remove_dups, apply_walk_updates, src)
+
+    def walk(self, walk_id: int) -> str:
+        """graph/wharfmh.h:365 for any global walk id: the owner broadcasts the text."""
+        owner = (walk_id % self.number_of_vertices()) % self.world
+        box = [self.engine.walk(walk_id) if self.rank == owner else None]
+        dist.broadcast_object_list(box, src=owner, group=self.group)
+        return box[0]
+
+    def local_walks(self) -> tuple[np.ndarray, np.ndarray]:
+        """(global ids, rows) of the walks this rank owns."""
+        return self.engine.local_walk_ids(), self.engine.walks()
+
+    def destroy(self) -> None:
+        self.engine.destroy()

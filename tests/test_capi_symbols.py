@@ -1,0 +1,81 @@
+"""CPU tests of the drop-in boundary: the shared library loads and exports every symbol include/wharfmh_b200.h
+declares; host-only entry points behave; compute entry points fail loudly without a GPU (no CPU fallback)."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+HEADER = ROOT / "include" / "wharfmh_b200.h"
+
+
+def declared_symbols():
+    text = HEADER.read_text()
+    return sorted(set(re.findall(r"WMH_API\s+[\w\s\*]+?\b(wmh_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_reference_surface():
+    syms = declared_symbols()
+    for must in ("wmh_create", "wmh_generate_initial_random_walks", "wmh_insert_edges_batch", "wmh_delete_edges_batch",
+                 "wmh_walk", "wmh_vertex_at_walk", "wmh_flatten_graph", "wmh_destroy", "wmh_destroy_index",
+                 "wmh_memory_footprint", "wmh_szudzik_pair_u64", "wmh_index_find_next", "wmh_compressed_find_next"):
+        assert must in syms
+    # every entry point cites the reference interface it replaces
+    text = HEADER.read_text()
+    for ref in ("graph/wharfmh.h:58", "graph/wharfmh.h:250", "graph/wharfmh.h:439", "graph/wharfmh.h:365", "walks/pairings.h",
+                "walks/inverted_index.h:74-92", "walks/compressed_walks.h", "config/globals.h:7-29"):
+        assert ref in text
+
+
+def test_library_exports_every_declared_symbol(wharf):
+    lib = wharf._capi.load()
+    syms = declared_symbols()
+    assert len(syms) >= 50
+    for name in syms:
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+        assert name in wharf._capi.SIGNATURES, f"{name} has no ctypes signature"
+    assert set(wharf._capi.SIGNATURES) == set(syms)
+
+
+def test_host_only_entry_points(wharf, golden):
+    lib = wharf._capi.load()
+    assert b"sm_100a" in lib.wmh_version()
+    cfg = wharf._capi.WmhConfig()
+    lib.wmh_default_config(C.byref(cfg))
+    # config/globals.h:7-29 defaults
+    assert (cfg.walks_per_vertex, cfg.walk_length, cfg.model, cfg.deterministic) == (10, 80, wharf.NODE2VEC, 1)
+    assert (cfg.param_p, cfg.param_q, cfg.init_strategy, cfg.world) == (4.0, 1.0, wharf.INIT_WEIGHT, 1)
+    # Szudzik host scalars: tests/pairings.cpp KATs and the reference's own outputs
+    assert wharf.szudzik_pair(65535, 65535) == 4294967295 and wharf.szudzik_unpair(4294967295) == (65535, 65535)
+    for x, y, z in golden["pair64"]:
+        assert wharf.szudzik_pair(x, y) == z and wharf.szudzik_unpair(z) == (x, y)
+    for z, x, y in golden["unpair64"]:
+        assert wharf.szudzik_unpair(z) == (x, y)
+    # exact above the reference's double-sqrt domain: z = s*s for large s decodes to (s, 0)
+    s = 2**32 - 3
+    assert wharf.szudzik_unpair(s * s) == (s, 0) and wharf.szudzik_unpair(s * s + s) == (0, s)
+    rng = np.random.default_rng(0)
+    for x, y in rng.integers(0, 2**32, (5000, 2), dtype=np.uint64):
+        assert wharf.szudzik_unpair(wharf.szudzik_pair(int(x), int(y))) == (int(x), int(y))
+
+
+def test_no_cpu_fallback(wharf):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(wharf.WharfError) as ei:
+        wharf.WharfMH(4, 0, np.zeros(4, dtype=np.uint64), np.zeros(0, dtype=np.uint32))
+    assert ei.value.code == wharf._capi.ERR_CUDA and "no CPU path" in str(ei.value)
+    lib = wharf._capi.load()
+    k = C.c_uint64()
+    assert lib.wmh_generate_batch_of_edges_device(0, 10, 17, 0, 0, 0, 0.5, 0.2, 0.1, C.c_void_p(8), C.byref(k)) == wharf._capi.ERR_CUDA
+    assert lib.wmh_generate_initial_random_walks(None) == wharf._capi.ERR_INVALID
+
+
+def test_product_never_touches_the_oracle():
+    pkg = ROOT / "dynamicgraphrepresentationlearning_b200"
+    for path in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")) + list(pkg.rglob("*.hpp")) + [ROOT / "include" / "wharfmh_b200.h"]:
+        text = path.read_text()
+        assert "wharf_oracle" not in text and "oracle/" not in text and "from oracle" not in text, path

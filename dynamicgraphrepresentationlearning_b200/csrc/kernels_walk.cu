@@ -10,6 +10,9 @@
 #include "engine.hpp"
 #include "rng.cuh"
 
+#include <cstdio>
+#include <cstdlib>
+
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
@@ -93,6 +96,71 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkP
         if (first == last) stopped = load_desc(p.desc, cur).degree == 0;   // resumed on the last cell: only the degree matters
         steps = pos - first + (stopped ? 0u : 1u);                   // the draw at the last position is unobservable (:315-317)
         for (++pos; pos <= last; ++pos, out += p.w_local) *out = kNoVertex;
+    }
+    block_add_u64(steps_out, steps);
+}
+
+// Bulk generation with kWalks independent walkers per thread (deterministic rule).  A walker step is two
+// dependent random loads (row descriptor, then one neighbour): with one walker per thread the SM holds at
+// most 2048 loads in flight, which leaves HBM latency-bound on graphs larger than L2.  Interleaving kWalks
+// walkers per thread multiplies the loads in flight without more threads.  Thread t owns local walks
+// t, t + T, t + 2T ... (T = threads in the grid) so every store stays coalesced.
+template <int kWalks, int kBlock, bool kStreamStore>
+__global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkParams p, u64 stride, unsigned long long* steps_out)
+{
+    const u64 t = (u64) blockIdx.x * kBlock + threadIdx.x;
+    u32 cur[kWalks];
+    u32 rep_off[kWalks];       // replica * L: offset of the walker's draw row
+    bool alive[kWalks];
+    u32 steps = 0;
+#pragma unroll
+    for (int k = 0; k < kWalks; k++)
+    {
+        const u64 w = t + (u64) k * stride;
+        alive[k] = w < p.w_local;
+        const u32 replica = alive[k] ? (u32) (w / p.n_local) : 0;
+        rep_off[k] = replica * p.L;
+        cur[k] = alive[k] ? (u32) (w - (u64) replica * p.n_local) * p.world + p.rank : 0;
+        if (alive[k]) p.walks[w] = cur[k];
+    }
+    bool live[kWalks];          // walker still moving (alive and not stopped on a degree-0 vertex)
+#pragma unroll
+    for (int k = 0; k < kWalks; k++) live[k] = alive[k];
+    const u32 last = p.L - 1;
+    u32* out = p.walks + p.w_local + t;
+    for (u32 pos = 0; pos < last; ++pos, out += p.w_local)
+    {
+        RowDesc d[kWalks];
+#pragma unroll
+        for (int k = 0; k < kWalks; k++) d[k] = live[k] ? load_desc(p.desc, cur[k]) : RowDesc{0, 0};
+        u32 nxt[kWalks];
+#pragma unroll
+        for (int k = 0; k < kWalks; k++)
+        {
+            nxt[k] = kNoVertex;
+            if (d[k].degree)
+            {
+                const u32 j = mod_u64_u32(__ldg(p.draw + rep_off[k] + pos), d[k].degree);
+                nxt[k] = __ldg(p.pool + d[k].begin + j);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < kWalks; k++)
+        {
+            if (alive[k])
+            {
+                if (kStreamStore) __stcs(out + (u64) k * stride, nxt[k]); else out[(u64) k * stride] = nxt[k];
+            }
+            steps += live[k] && d[k].degree;
+            live[k] = live[k] && d[k].degree;
+            cur[k] = nxt[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kWalks; k++)
+    {
+        if (p.L == 1) live[k] = alive[k] && load_desc(p.desc, cur[k]).degree;
+        steps += live[k];                                      // the unobservable draw at the last position (:315-317)
     }
     block_add_u64(steps_out, steps);
 }
@@ -347,12 +415,49 @@ DevWalkParams to_dev(const WalkParams& wp)
     return p;
 }
 
+// Tuning knobs of the bulk deterministic kernel: walkers per thread / block size / streaming stores.
+// Defaults are the measured best on B200 (profiles/); WHARF_DET_VARIANT="walks,block,stream" overrides for sweeps.
+struct DetVariant { int walks = 1, block = 256, stream = 0; };
+
+DetVariant det_variant()
+{
+    DetVariant v;
+    if (const char* e = std::getenv("WHARF_DET_VARIANT")) std::sscanf(e, "%d,%d,%d", &v.walks, &v.block, &v.stream);
+    return v;
+}
+
+template <int kWalks, int kBlock, bool kStream>
+void launch_det_ilp(const LaunchCtx& lc, const DevWalkParams& p, unsigned long long* d_steps)
+{
+    const u64 threads = (p.w_local + kWalks - 1) / kWalks;
+    const unsigned grid = div_up(threads, kBlock);
+    const u64 stride = (u64) grid * kBlock;
+    walk_deterministic_ilp_kernel<kWalks, kBlock, kStream><<<grid, kBlock, 0, lc.stream>>>(p, stride, d_steps);
+}
+
+void launch_generate_deterministic(const LaunchCtx& lc, const DevWalkParams& p, unsigned long long* d_steps)
+{
+    const DetVariant v = det_variant();
+#define WHARF_DET_CASE(W, B, S) if (v.walks == W && v.block == B && v.stream == S) { launch_det_ilp<W, B, S != 0>(lc, p, d_steps); lc.count(); WHARF_CUDA(cudaGetLastError()); return; }
+    WHARF_DET_CASE(1, 256, 0) WHARF_DET_CASE(1, 256, 1) WHARF_DET_CASE(1, 128, 0) WHARF_DET_CASE(1, 512, 0) WHARF_DET_CASE(1, 1024, 0)
+    WHARF_DET_CASE(2, 256, 0) WHARF_DET_CASE(2, 256, 1) WHARF_DET_CASE(2, 128, 1) WHARF_DET_CASE(2, 512, 1)
+    WHARF_DET_CASE(4, 256, 0) WHARF_DET_CASE(4, 256, 1) WHARF_DET_CASE(4, 128, 1) WHARF_DET_CASE(4, 512, 1)
+    WHARF_DET_CASE(8, 256, 1) WHARF_DET_CASE(8, 128, 1)
+#undef WHARF_DET_CASE
+    throw CudaError(cudaErrorInvalidValue, "unsupported WHARF_DET_VARIANT");
+}
+
 template <bool kRewalk>
 void launch_walk(const LaunchCtx& lc, const WalkParams& wp, const u32* ids, const u32* positions, u64 count, unsigned long long* d_steps)
 {
     if (count == 0) return;
     const DevWalkParams p = to_dev(wp);
     const unsigned grid = div_up(count, kWalkBlock);
+    if (wp.deterministic && !kRewalk && det_variant().walks != 0)
+    {
+        launch_generate_deterministic(lc, p, d_steps);
+        return;
+    }
     if (wp.deterministic)
         walk_deterministic_kernel<kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
     else if (wp.model == WMH_NODE2VEC)

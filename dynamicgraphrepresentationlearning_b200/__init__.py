@@ -5,11 +5,11 @@ Public surface = the reference's (dygrl::WharfMH + namespace config), see wharfm
 raises.
 """
 from . import _capi
-from ._capi import (DEEPWALK, INIT_BURNIN, INIT_RANDOM, INIT_WEIGHT, NODE2VEC, NO_VERTEX, REF_SENTINEL, SEARCH_AUTO,
+from ._capi import (DEEPWALK, GENERATE_AUTO, GENERATE_COALESCED, GENERATE_PER_WALKER, INIT_BURNIN, INIT_RANDOM, INIT_WEIGHT, NODE2VEC, NO_VERTEX, REF_SENTINEL, SEARCH_AUTO,
                     SEARCH_INDEX, SEARCH_SCAN, WharfError)
-from .wharfmh import Config, WharfMH, szudzik_pair, szudzik_unpair
+from .wharfmh import Config, WharfMH, szudzik_pair, szudzik_unpair, trim_memory
 
 _capi.load()   # fail loudly at import when the CUDA library is missing
 
 __all__ = ["Config", "WharfMH", "WharfError", "DEEPWALK", "NODE2VEC", "INIT_RANDOM", "INIT_BURNIN", "INIT_WEIGHT",
-           "SEARCH_AUTO", "SEARCH_INDEX", "SEARCH_SCAN", "NO_VERTEX", "REF_SENTINEL", "szudzik_pair", "szudzik_unpair"]
+           "SEARCH_AUTO", "SEARCH_INDEX", "SEARCH_SCAN", "GENERATE_AUTO", "GENERATE_PER_WALKER", "GENERATE_COALESCED", "NO_VERTEX", "REF_SENTINEL", "szudzik_pair", "szudzik_unpair", "trim_memory"]

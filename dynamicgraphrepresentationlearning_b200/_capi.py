@@ -19,6 +19,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_DOMAIN, ERR_RANGE = range(7)
 DEEPWALK, NODE2VEC = 0, 1
 INIT_RANDOM, INIT_BURNIN, INIT_WEIGHT = 0, 1, 2
 SEARCH_AUTO, SEARCH_INDEX, SEARCH_SCAN = 0, 1, 2
+GENERATE_AUTO, GENERATE_PER_WALKER, GENERATE_COALESCED = 0, 1, 2
 TIMER_GRAPH_UPDATE_INSERT, TIMER_WALK_UPDATE_INSERT, TIMER_GRAPH_UPDATE_DELETE, TIMER_WALK_UPDATE_DELETE, TIMER_GENERATE = range(5)
 
 
@@ -37,7 +38,7 @@ class WmhConfig(C.Structure):
         ("device", C.c_int32),
         ("rank", C.c_uint32),
         ("world", C.c_uint32),
-        ("reserved", C.c_uint32),
+        ("generate_mode", C.c_uint32),
     ]
 
 
@@ -110,6 +111,7 @@ SIGNATURES = {
     "wmh_device_walks": (vp, [vp]),
     "wmh_stream": (vp, [vp]),
     "wmh_synchronize": (i32, [vp]),
+    "wmh_trim_memory": (i32, [i32]),
     "wmh_generate_batch_of_edges_device": (i32, [i32, u64, u64, u64, i32, i32, C.c_double, C.c_double, C.c_double, vp, PU64]),
     "wmh_pairs_to_csr_device": (i32, [i32, u64, vp, u64, vp, vp]),
 }

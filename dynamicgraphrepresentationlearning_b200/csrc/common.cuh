@@ -52,20 +52,29 @@ inline unsigned grid_for(u64 work_items, unsigned block, unsigned blocks_per_sm,
     return (unsigned) (need < full ? need : full);
 }
 
-// Owning device allocation (cudaMalloc).  Not copyable.
+// Stream on which DeviceBuffer allocates and frees (cudaMallocAsync / cudaFreeAsync).  An engine sets it to its
+// own stream while it runs (wmh_engine::bind); with no stream set the buffers fall back to cudaMalloc/cudaFree.
+// Stream-ordered allocation keeps engine create/destroy and pool growth out of the driver's synchronous
+// allocator: freed blocks stay in the device memory pool (release threshold = max) and are handed out again.
+inline thread_local cudaStream_t g_alloc_stream = nullptr;
+inline thread_local bool g_alloc_async = false;
+
+// Owning device allocation.  Not copyable.
 template <class T>
 struct DeviceBuffer
 {
     T*  ptr = nullptr;
     u64 count = 0;
+    cudaStream_t stream = nullptr;   // stream the block was allocated on (async blocks only)
+    bool async = false;
 
     DeviceBuffer() = default;
     DeviceBuffer(const DeviceBuffer&) = delete;
     DeviceBuffer& operator=(const DeviceBuffer&) = delete;
-    DeviceBuffer(DeviceBuffer&& o) noexcept : ptr(o.ptr), count(o.count) { o.ptr = nullptr; o.count = 0; }
+    DeviceBuffer(DeviceBuffer&& o) noexcept : ptr(o.ptr), count(o.count), stream(o.stream), async(o.async) { o.ptr = nullptr; o.count = 0; }
     DeviceBuffer& operator=(DeviceBuffer&& o) noexcept
     {
-        if (this != &o) { release(); ptr = o.ptr; count = o.count; o.ptr = nullptr; o.count = 0; }
+        if (this != &o) { release(); ptr = o.ptr; count = o.count; stream = o.stream; async = o.async; o.ptr = nullptr; o.count = 0; }
         return *this;
     }
     ~DeviceBuffer() { release(); }
@@ -74,19 +83,21 @@ struct DeviceBuffer
     {
         release();
         if (n == 0) return;
-        cudaError_t e = cudaMalloc((void**) &ptr, n * sizeof(T));
+        async = g_alloc_async;
+        stream = g_alloc_stream;
+        cudaError_t e = async ? cudaMallocAsync((void**) &ptr, n * sizeof(T), stream) : cudaMalloc((void**) &ptr, n * sizeof(T));
         if (e != cudaSuccess)
         {
             ptr = nullptr;
             cudaGetLastError();
-            throw CudaError(e, "cudaMalloc of " + std::to_string(n * sizeof(T)) + " bytes failed: " + cudaGetErrorString(e));
+            throw CudaError(e, "device allocation of " + std::to_string(n * sizeof(T)) + " bytes failed: " + cudaGetErrorString(e));
         }
         count = n;
     }
     void ensure(u64 n) { if (n > count) allocate(n); }
     void release()
     {
-        if (ptr) cudaFree(ptr);
+        if (ptr) { if (async) cudaFreeAsync(ptr, stream); else cudaFree(ptr); }
         ptr = nullptr;
         count = 0;
     }

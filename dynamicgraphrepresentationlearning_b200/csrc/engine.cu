@@ -58,6 +58,7 @@ struct wmh_engine
 
     DeviceGraph g;
     DeviceBuffer<u64> draw;            // X[wpv][L]
+    std::vector<u64> host_draw;        // the same table on the host (kernel arguments of the coalesced path)
     u32 draw_wpv = 0, draw_len = 0;
 
     DeviceBuffer<u32> walks;           // [L][w_local]
@@ -85,7 +86,12 @@ struct wmh_engine
     DeviceBuffer<u32> small;           // misc tiny results
 
     LaunchCtx lc() { return LaunchCtx{stream, sm_count, &launches, &library_calls}; }
-    void bind() const { WHARF_CUDA(cudaSetDevice(cfg.device)); }
+    void bind() const
+    {
+        WHARF_CUDA(cudaSetDevice(cfg.device));
+        g_alloc_stream = stream;          // DeviceBuffer allocations of this thread are ordered on the engine stream
+        g_alloc_async = stream != nullptr;
+    }
 
     ~wmh_engine()
     {
@@ -105,6 +111,7 @@ void validate_config(const wmh_config& c)
     if (c.model > WMH_NODE2VEC) throw std::invalid_argument("unrecognized random walking model");          // wharfmh.h:269-271
     if (c.init_strategy > WMH_INIT_WEIGHT) throw std::invalid_argument("unrecognized sampler init strategy");
     if (c.search_mode > WMH_SEARCH_SCAN) throw std::invalid_argument("unrecognized search mode");
+    if (c.generate_mode > WMH_GENERATE_COALESCED) throw std::invalid_argument("unrecognized generate mode");
     if (c.world == 0 || c.rank >= c.world) throw std::invalid_argument("rank must be < world, world >= 1");
     if (c.model == WMH_NODE2VEC && !c.deterministic && (!(c.param_p > 0) || !(c.param_q > 0))) throw std::invalid_argument("node2vec p and q must be positive");
 }
@@ -137,6 +144,7 @@ std::unique_ptr<wmh_engine> make_engine(const wmh_config* cfg)
         cudaGetLastError();
     }
     WHARF_CUDA(cudaStreamCreateWithFlags(&eng->stream, cudaStreamNonBlocking));
+    eng->bind();
     for (auto& ev : eng->ev) WHARF_CUDA(cudaEventCreate(&ev));
     // keep stream-ordered scratch in the pool between batches
     cudaMemPool_t pool;
@@ -209,6 +217,15 @@ void ensure_memo(wmh_engine& e)
     }
 }
 
+// Deterministic bulk generation: the coalesced schedule pays ~6 small launches per position, the per-walker kernel
+// two random loads per step; the latter wins while descriptors + neighbours stay in the 126 MB L2.
+bool use_coalesced(const wmh_engine& e)
+{
+    if (!e.cfg.deterministic || e.cfg.generate_mode == WMH_GENERATE_PER_WALKER) return false;
+    if (e.cfg.generate_mode == WMH_GENERATE_COALESCED) return true;
+    return e.g.n * sizeof(RowDesc) + e.g.m * sizeof(u32) > (96ull << 20);
+}
+
 void generate(wmh_engine& e)
 {
     e.bind();
@@ -228,7 +245,8 @@ void generate(wmh_engine& e)
     e.min_pos.ensure(std::max<u64>(1, e.w_local));
     if (e.draw_wpv != wpv || e.draw_len != L)
     {
-        const std::vector<u64> table = make_draw_table(wpv, L);
+        e.host_draw = make_draw_table(wpv, L);
+        const std::vector<u64>& table = e.host_draw;
         e.draw.allocate(table.size());
         WHARF_CUDA(cudaMemcpyAsync(e.draw.ptr, table.data(), table.size() * sizeof(u64), cudaMemcpyHostToDevice, e.stream));
         WHARF_CUDA(cudaStreamSynchronize(e.stream));
@@ -242,7 +260,8 @@ void generate(wmh_engine& e)
     }
     WHARF_CUDA(cudaMemsetAsync(e.d_steps.ptr, 0, 8, e.stream));
     WHARF_CUDA(cudaEventRecord(e.ev[0], e.stream));
-    walks_generate(lc, walk_params(e), e.d_steps.ptr);
+    if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr);
+    else walks_generate(lc, walk_params(e), e.d_steps.ptr);
     WHARF_CUDA(cudaEventRecord(e.ev[1], e.stream));
     unsigned long long steps = 0;
     WHARF_CUDA(cudaMemcpyAsync(&steps, e.d_steps.ptr, 8, cudaMemcpyDeviceToHost, e.stream));
@@ -524,6 +543,8 @@ void wmh_destroy(wmh_engine* e)
     cudaStream_t s = e->stream;
     int device = e->cfg.device;
     delete e;
+    g_alloc_stream = nullptr;
+    g_alloc_async = false;
     cudaSetDevice(device);
     if (s) cudaStreamDestroy(s);
 }
@@ -973,6 +994,18 @@ int wmh_synchronize(wmh_engine* e)
     return guarded([&] {
         e->bind();
         WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_trim_memory(int device)
+{
+    return guarded([&] {
+        DefaultCtx ctx(device);
+        WHARF_CUDA(cudaDeviceSynchronize());
+        cudaMemPool_t pool;
+        WHARF_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        WHARF_CUDA(cudaMemPoolTrimTo(pool, 0));
         return (int) WMH_OK;
     });
 }

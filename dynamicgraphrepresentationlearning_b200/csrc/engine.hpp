@@ -114,6 +114,9 @@ struct WalkParams
 void walks_generate(const LaunchCtx& lc, const WalkParams& wp, unsigned long long* d_steps);
 void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affected, const u32* d_positions, u64 count,
                   unsigned long long* d_steps);
+// Deterministic mode only: step-synchronous generation that advances walkers standing on the same vertex once
+// (kernels_coalesced.cu).  host_draw = X[wpv][L] on the host.
+void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps);
 // min_pos[w] = first position whose vertex is in the touched bitmap (kNoPos when none).
 void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_bitmap, u32* d_min_pos);
 // Compacts min_pos != kNoPos into (ids, positions); returns the count.

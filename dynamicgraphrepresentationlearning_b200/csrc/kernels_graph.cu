@@ -11,6 +11,10 @@
 // pool fills.  Rows are always ascending and unique, which is all the walk path needs from the C-tree.
 #include "engine.hpp"
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
@@ -18,6 +22,28 @@
 
 namespace wharf
 {
+// WHARF_TRACE=1: host-timed phases with the stream synchronised at every mark; WHARF_TRACE=2: host time between
+// marks without synchronising (shows where the submitting thread blocks).  Tuning aid only, stderr.
+struct Trace
+{
+    cudaStream_t stream;
+    int mode;
+    std::chrono::steady_clock::time_point t0;
+    explicit Trace(cudaStream_t s) : stream(s), mode(std::getenv("WHARF_TRACE") ? std::atoi(std::getenv("WHARF_TRACE")) : 0)
+    {
+        if (mode == 1) cudaStreamSynchronize(s);
+        if (mode) t0 = std::chrono::steady_clock::now();
+    }
+    void mark(const char* what)
+    {
+        if (!mode) return;
+        if (mode == 1) cudaStreamSynchronize(stream);
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[wharf trace] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 namespace
 {
 constexpr u32 kChunk = 1024;      // old-row elements copied by one warp in the merge
@@ -179,19 +205,18 @@ __global__ void commit_rows_kernel(const u32* __restrict__ sources, u64 n_source
     if (bitmap) atomicOr(bitmap + (v >> 5), 1u << (v & 31));
 }
 
-// The sampler cache of state (c, prev = t) depends on N(t): after t's row changed, empty the slot of t in
-// every row c in N(t).  One thread per element of the freshly written rows.
-__global__ void invalidate_memo_kernel(const u32* __restrict__ sources, u64 n_sources, const u64* __restrict__ alloc_scan, u64 total,
-                                       u64 pool_base, const RowDesc* __restrict__ desc, const u32* __restrict__ pool, u32* __restrict__ memo)
+// The sampler cache word of state (cur, prev) sits in the slot of cur in the row of prev (kernels_walk.cu) and is a
+// function of the rows of cur and prev and of version[cur].  Rows re-written by the batch start with an empty
+// cache; this pass empties every other word whose cur is a batch source (bit set in the touched bitmap).  One
+// streaming pass over the used part of the pool: it needs no reverse adjacency, so it is exact for directed graphs.
+__global__ void __launch_bounds__(256) invalidate_memo_stream_kernel(const u32* __restrict__ pool, u64 used, const u32* __restrict__ bitmap,
+                                                                     u32* __restrict__ memo)
 {
-    const u64 e = (u64) blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= total) return;
-    const u32 j = upper_segment_u64(alloc_scan, (u32) n_sources + 1, e);
-    const u32 t = sources[j];
-    const u32 c = pool[pool_base + e];
-    const uint2 dc = reinterpret_cast<const uint2*>(desc)[c];
-    const u32 i = lower_bound_u32(pool + dc.x, dc.y, t);
-    if (i < dc.y && pool[dc.x + i] == t) memo[dc.x + i] = kNoVertex;
+    for (u64 e = (u64) blockIdx.x * 256 + threadIdx.x; e < used; e += (u64) gridDim.x * 256)
+    {
+        const u32 c = __ldcs(pool + e);
+        if ((__ldg(bitmap + (c >> 5)) >> (c & 31)) & 1u) memo[e] = 0xFFFFFFFFu;
+    }
 }
 
 // ---- row copy (compaction / export) ---------------------------------------------------------------
@@ -392,6 +417,7 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
     out.k = 0;
     out.n_sources = 0;
     if (count == 0) return;
+    Trace tr(lc.stream);
     Scratch<u64> raw(lc.stream, count), sorted(lc.stream, count);
     pairs_to_keys_kernel<<<div_up(count, 256), 256, 0, lc.stream>>>(d_pairs, count, raw.ptr);
     lc.count();
@@ -407,6 +433,7 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
     WHARF_CUDA(cudaGetLastError());
     out.keys.allocate(lc.stream, count);
     out.k = select_flagged(lc, sorted.ptr, flags.ptr, count, out.keys.ptr);
+    tr.mark("prepare: sort+dedup");
     if (out.k == 0) return;
 
     head_flags_kernel<<<div_up(out.k, 256), 256, 0, lc.stream>>>(out.keys.ptr, out.k, flags.ptr);
@@ -424,6 +451,7 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
         WHARF_CUDA(cudaMemcpyAsync(&out.n_sources, d_count.ptr, 8, cudaMemcpyDeviceToHost, lc.stream));
         WHARF_CUDA(cudaStreamSynchronize(lc.stream));
     }
+    tr.mark("prepare: slices");
     out.sources.allocate(lc.stream, out.n_sources);
     sources_kernel<<<div_up(out.n_sources, 256), 256, 0, lc.stream>>>(out.keys.ptr, out.slice.ptr, out.n_sources, out.k, out.sources.ptr);
     lc.count();
@@ -437,24 +465,30 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity)
     capacity += capacity / 2 + (1u << 20);
     if (capacity >= (1ull << 32)) capacity = (1ull << 32) - 1;
     if (g.m + extra_capacity > capacity) throw CudaError(cudaErrorMemoryAllocation, "neighbour pool would exceed 2^32 entries");
+    Trace tr(lc.stream);
     Scratch<u64> deg(lc.stream, g.n + 1), begin(lc.stream, g.n + 1);
     degrees_kernel<<<div_up(g.n + 1, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, deg.ptr);
     lc.count();
     exclusive_sum(lc, deg.ptr, begin.ptr, g.n + 1);
+    tr.mark("compact: degrees+scan");
     DeviceBuffer<u32> fresh;
     fresh.allocate(capacity);
+    tr.mark("compact: cudaMalloc pool");
     copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, begin.ptr, fresh.ptr);
+    tr.mark("compact: copy_all_rows");
     repoint_kernel<<<div_up(g.n, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, begin.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
     g.pool = std::move(fresh);
     g.pool_used = g.m;
+    tr.mark("compact: repoint+free old");
     if (g.memo.ptr)
     {
         // the cache holds pure functions of (graph, key): dropping it is always safe
         g.memo.allocate(capacity);
         WHARF_CUDA(cudaMemsetAsync(g.memo.ptr, 0xFF, capacity * sizeof(u32), lc.stream));
+        tr.mark("compact: memo realloc");
     }
 }
 
@@ -462,6 +496,7 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
 {
     if (b.k == 0) return;
     const u64 k = b.k, ns = b.n_sources;
+    Trace tr(lc.stream);
     Scratch<u32> rank(lc.stream, k), change(lc.stream, k + 1);
     Scratch<u64> change_scan(lc.stream, k + 1);
     locate_kernel<<<div_up(k + 1, 256), 256, 0, lc.stream>>>(b.keys.ptr, k, g.desc.ptr, g.pool.ptr, is_delete, rank.ptr, change.ptr);
@@ -483,9 +518,11 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     WHARF_CUDA(cudaMemcpyAsync(&totals[2], change_scan.ptr + k, 8, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
     const u64 total = totals[0], n_chunks = totals[1], changed = totals[2];
+    tr.mark("apply: locate+plan");
 
     if (g.pool_used + total > g.pool.count) graph_compact(lc, g, total);    // rank[] is row-relative: still valid
     const u64 base = g.pool_used;
+    tr.mark("apply: compact (if any)");
 
     if (n_chunks)
     {
@@ -504,14 +541,19 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
                                                                g.version.ptr, d_touched_bitmap);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
-    if (g.memo.ptr && total)
+    tr.mark("apply: merge+write+commit");
+    if (g.memo.ptr)
     {
-        WHARF_CUDA(cudaMemsetAsync(g.memo.ptr + base, 0xFF, total * sizeof(u32), lc.stream));   // fresh rows: empty cache
-        invalidate_memo_kernel<<<div_up(total, 256), 256, 0, lc.stream>>>(b.sources.ptr, ns, alloc_scan.ptr, total, base, g.desc.ptr,
-                                                                          g.pool.ptr, g.memo.ptr);
-        lc.count();
-        WHARF_CUDA(cudaGetLastError());
+        if (total) WHARF_CUDA(cudaMemsetAsync(g.memo.ptr + base, 0xFF, total * sizeof(u32), lc.stream));   // fresh rows: empty cache
+        if (d_touched_bitmap && base)
+        {
+            invalidate_memo_stream_kernel<<<grid_for(base, 256, 8, lc.sm_count), 256, 0, lc.stream>>>(g.pool.ptr, base, d_touched_bitmap, g.memo.ptr);
+            lc.count();
+            WHARF_CUDA(cudaGetLastError());
+        }
+        else if (!d_touched_bitmap) WHARF_CUDA(cudaMemsetAsync(g.memo.ptr, 0xFF, g.memo.bytes(), lc.stream));
     }
+    tr.mark("apply: memo invalidation");
     g.pool_used += total;
     g.m = is_delete ? g.m - changed : g.m + changed;
 }

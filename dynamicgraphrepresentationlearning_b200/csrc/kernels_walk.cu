@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkP
             cur = __ldg(p.pool + d.begin + j);
             *out = cur;
         }
-        if (first == last) stopped = load_desc(p.desc, cur).degree == 0;   // resumed on the last cell: only the degree matters
+        if (!stopped) stopped = load_desc(p.desc, cur).degree == 0;  // last cell: only the degree matters
         steps = pos - first + (stopped ? 0u : 1u);                   // the draw at the last position is unobservable (:315-317)
         for (++pos; pos <= last; ++pos, out += p.w_local) *out = kNoVertex;
     }
@@ -159,27 +159,58 @@ __global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkP
 #pragma unroll
     for (int k = 0; k < kWalks; k++)
     {
-        if (p.L == 1) live[k] = alive[k] && load_desc(p.desc, cur[k]).degree;
+        if (live[k]) live[k] = load_desc(p.desc, cur[k]).degree != 0;
         steps += live[k];                                      // the unobservable draw at the last position (:315-317)
     }
     block_add_u64(steps_out, steps);
 }
 
 // ---- Metropolis-Hastings mode ------------------------------------------------------------------------
+//
+// Sampler cache ("memo").  The sampler of state (cur, prev) lives in cur's SamplerManager (graph/vertex.h:12) and,
+// because find() hands out copies (wharfmh.h:301,833), never advances past its init value
+// (metropolis_hastings_sampler.h:69-108), a pure function of (seed, cur, prev, version[cur]) and the rows of cur
+// and prev.  A walker in state (cur, prev) has just traversed the edge prev -> cur, whose slot in the row of
+// prev it knows (it picked it), so the cache word of the state lives at memo[begin(prev) + slot]:
+//     bits 0..29  slot of the init value in the row of cur        (vertex = pool[begin(cur) + slot])
+//     bits 30..31 weight class of the init value with respect to prev (node2vec.h:74-88)
+//     0xFFFFFFFF  empty
+// The word dies with the row of prev (fresh rows start empty) and is emptied by invalidate_memo_stream_kernel
+// whenever cur is a batch source (row and version[cur] change, wharfmh.h:504->539).
+constexpr u32 kMemoEmpty = 0xFFFFFFFFu;
+constexpr u32 kNoSlot    = 0xFFFFFFFFu;
+constexpr u32 kSlotMask  = 0x3FFFFFFFu;
+enum : u32 { kClassReturn = 0, kClassNeighbour = 1, kClassFar = 2 };   // 1/p, 1, 1/q
 
-__device__ __forceinline__ bool row_contains(const u32* __restrict__ pool, RowDesc d, u32 key, u32* index)
+__device__ __forceinline__ float class_weight(const DevWalkParams& p, u32 cls)
 {
-    const u32 i = lower_bound_u32(pool + d.begin, d.degree, key);      // node2vec.h:112-119 (std::binary_search)
-    *index = i;
-    return i < d.degree && __ldg(pool + d.begin + i) == key;
+    return cls == kClassReturn ? p.inv_p : (cls == kClassNeighbour ? 1.0f : p.inv_q);
 }
 
-// Node2Vec::weight - walks/models/node2vec.h:74-88; state = (cur, prev), dprev = row of prev.
-__device__ __forceinline__ float n2v_weight(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x)
+// Index of the last element <= key of an ascending row (0 when there is none); branch-free halving, one load per
+// level.  *hit = whether that element equals key (std::binary_search of node2vec.h:112-119).
+__device__ __forceinline__ u32 row_find(const u32* __restrict__ row, u32 n, u32 key, bool* hit)
 {
-    if (x == prev) return p.inv_p;
-    u32 ignore;
-    return row_contains(p.pool, dprev, x, &ignore) ? 1.0f : p.inv_q;
+    u32 base = 0;
+    *hit = false;
+    if (n == 0) return 0;
+    while (n > 1)
+    {
+        const u32 half = n >> 1;
+        if (__ldg(row + base + half) <= key) base += half;
+        n -= half;
+    }
+    *hit = __ldg(row + base) == key;
+    return base;
+}
+
+// Node2Vec::weight as a class - walks/models/node2vec.h:74-88; state = (cur, prev), dprev = row of prev.
+__device__ __forceinline__ u32 n2v_class(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x)
+{
+    if (x == prev) return kClassReturn;
+    bool hit;
+    row_find(p.pool + dprev.begin, dprev.degree, x, &hit);
+    return hit ? kClassNeighbour : kClassFar;
 }
 
 // MetropolisHastingsSampler::accept - walks/metropolis_hastings_sampler.h:118-122.
@@ -189,113 +220,196 @@ __device__ __forceinline__ bool mh_accept(float w_old, float w_new, u64 draw)
     return unit_double(draw) <= (double) w_new / (double) w_old;
 }
 
-// MetropolisHastingsSampler::init - walks/metropolis_hastings_sampler.h:69-108, draws keyed by
-// (seed, cur, prev, version[cur], i).
-__device__ u32 n2v_sampler_init(const DevWalkParams& p, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
+// MetropolisHastingsSampler::init, strategies RANDOM and BURNIN (metropolis_hastings_sampler.h:72-85), one lane;
+// draws keyed by (seed, cur, prev, version[cur], i).  Returns the cache word.
+__device__ u32 n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
 {
     const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
     u64 i = 0;
     const u32* __restrict__ nb = p.pool + dcur.begin;
-    u32 last = __ldg(nb + mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree));   // RANDOM :72-75
-    if (p.init_strategy == WMH_INIT_BURNIN)                                                               // :77-85
+    u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);                 // RANDOM :72-75
+    u32 cls = n2v_class(p, prev, dprev, __ldg(nb + slot));
+    if (p.init_strategy == WMH_INIT_BURNIN)                                                                // :77-85
     {
         for (int it = 0; it < 100; it++)
         {
-            const u32 cand = __ldg(nb + mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree));
-            const float wn = n2v_weight(p, prev, dprev, cand), wo = n2v_weight(p, prev, dprev, last);
+            const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);
+            const u32 ccls = n2v_class(p, prev, dprev, __ldg(nb + cslot));
+            const float wn = class_weight(p, ccls), wo = class_weight(p, cls);
             bool acc = wo < wn;
             if (!acc) acc = unit_double(keyed_draw(p.seed, kDomSampler, cur, key_b, i++)) <= (double) wn / (double) wo;
-            if (acc) last = cand;
+            if (acc) { slot = cslot; cls = ccls; }
         }
     }
-    else if (p.init_strategy == WMH_INIT_WEIGHT)                                                          // :87-107
-    {
-        u32 best = last;
-        float best_w = n2v_weight(p, prev, dprev, best);
-        for (int it = 0; it < 20; it++)
-        {
-            const u32 cand = __ldg(nb + mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree));
-            const float w = n2v_weight(p, prev, dprev, cand);
-            if (w > best_w) { best_w = w; best = cand; }
-        }
-        last = best;
-    }
-    return last;
+    return (cls << 30) | slot;
 }
 
-// kModel: WMH_DEEPWALK / WMH_NODE2VEC.  One walker per thread; the prev-neighbour test is a per-thread
-// binary search over the ascending row of prev.
-template <int kModel, bool kRewalk>
-__global__ void __launch_bounds__(kWalkBlock) walk_mh_kernel(DevWalkParams p, const u32* __restrict__ affected,
-                                                             const u32* __restrict__ positions, u64 count,
-                                                             unsigned long long* steps_out)
+// MetropolisHastingsSampler::init, strategy WEIGHT (:87-107): the best of 1 + 20 proposals, a strict '>' keeps
+// the first maximum.  Warp-cooperative: the 21 proposals are independent draws (i = 0..20), so lane i evaluates
+// proposal i (one neighbour load + one row search) and a butterfly picks (largest weight, smallest i).
+// All 32 lanes call this with the broadcast state of the walker being served.
+__device__ __forceinline__ u32 n2v_init_weight_warp(const DevWalkParams& p, u32 lane, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
+{
+    const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
+    float w = -1.0f;
+    u32 word = kMemoEmpty;
+    if (lane < 21)
+    {
+        const u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, lane), dcur.degree);
+        const u32 cls = n2v_class(p, prev, dprev, __ldg(p.pool + dcur.begin + slot));
+        w = class_weight(p, cls);
+        word = (cls << 30) | slot;
+    }
+    u32 idx = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const float ow = __shfl_xor_sync(0xffffffffu, w, o);
+        const u32 oword = __shfl_xor_sync(0xffffffffu, word, o);
+        const u32 oidx = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ow > w || (ow == w && oidx < idx)) { w = ow; word = oword; idx = oidx; }
+    }
+    return word;
+}
+
+__device__ __forceinline__ u32 warp_max_u32(u32 v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// node2vec in MH mode (node2vec.h:42-119 + metropolis_hastings_sampler.h:31-46), one walker per thread.
+// The warp stays converged over a warp-uniform trip count (lanes without work are predicated off) so that the
+// WEIGHT sampler init can be served by all 32 lanes.  Per step a walker issues: the proposal load, the cache
+// word (address known from the previous step), one row search for the proposal's weight (per-thread binary
+// search over the ascending row of prev; 32 independent chains per warp keep more loads in flight than a
+// k-ary cooperative search that serialises the warp's queries), and the descriptor of the proposal
+// (speculative: it is the next cur unless the proposal is rejected).  The descriptor of prev is carried.
+template <bool kRewalk>
+__global__ void __launch_bounds__(kWalkBlock) walk_n2v_kernel(DevWalkParams p, const u32* __restrict__ affected,
+                                                              const u32* __restrict__ positions, u64 count,
+                                                              unsigned long long* steps_out)
+{
+    const u64 t = (u64) blockIdx.x * kWalkBlock + threadIdx.x;
+    const u32 lane = threadIdx.x & 31;
+    const bool owner = t < count;
+    const u32 last_pos = p.L - 1;
+    u64 w = 0, walk_id = 0;
+    u32 pos = 0, cur = 0, prev = 0, slot = kNoSlot;        // slot: index of cur in the row of prev
+    RowDesc d{0, 0}, dprev{0, 0};
+    if (owner)
+    {
+        if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = t; }
+        const u32 replica = (u32) (w / p.n_local);
+        const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
+        walk_id = (u64) replica * p.n + start;                       // global id keys the draws
+        if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
+        else { cur = start; p.walks[w] = cur; }
+        d = load_desc(p.desc, cur);
+        prev = cur;
+        if (pos > 0) prev = p.walks[(u64) (pos - 1) * p.w_local + w];                                  // wharfmh.h:819-823
+        else if (d.degree) prev = __ldg(p.pool + d.begin + mod_u64_u32(keyed_draw(p.seed, kDomState, walk_id, 0, 0), d.degree));   // node2vec.h:42-49
+        dprev = load_desc(p.desc, prev);
+        bool hit;
+        const u32 i = row_find(p.pool + dprev.begin, dprev.degree, cur, &hit);   // absent in a directed graph or after a delete
+        if (hit) slot = i;
+    }
+    const u32 first = pos;
+    u32* out = p.walks + (u64) (pos + 1) * p.w_local + w;
+    const u32 trips = warp_max_u32(owner ? last_pos - pos : 0u);
+    bool stopped = false;
+    for (u32 k = 0; k < trips; k++)
+    {
+        bool step = owner && !stopped && pos < last_pos;
+        if (step && d.degree == 0) { stopped = true; step = false; }              // isolated start (:277-286) or sink
+        u32 cand = 0, cslot = 0, word = kMemoEmpty, cls_new = kClassFar;
+        RowDesc dcand{0, 0};
+        if (step)
+        {
+            if (slot != kNoSlot) word = __ldcg(p.memo + dprev.begin + slot);
+            cslot = mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree);   // propose_vertex - node2vec.h:97-105
+            cand = __ldg(p.pool + d.begin + cslot);
+            dcand = load_desc(p.desc, cand);
+            cls_new = n2v_class(p, prev, dprev, cand);
+        }
+        const bool need = step && word == kMemoEmpty;
+        if (p.init_strategy == WMH_INIT_WEIGHT)
+        {
+            u32 pending = __ballot_sync(0xffffffffu, need);
+            while (pending)
+            {
+                const int src = __ffs(pending) - 1;
+                pending &= pending - 1;
+                const u32 s_cur = __shfl_sync(0xffffffffu, cur, src), s_prev = __shfl_sync(0xffffffffu, prev, src);
+                const RowDesc s_d{__shfl_sync(0xffffffffu, d.begin, src), __shfl_sync(0xffffffffu, d.degree, src)};
+                const RowDesc s_dp{__shfl_sync(0xffffffffu, dprev.begin, src), __shfl_sync(0xffffffffu, dprev.degree, src)};
+                const u32 r = n2v_init_weight_warp(p, lane, s_cur, s_d, s_prev, s_dp);
+                if ((int) lane == src) word = r;
+            }
+        }
+        else if (need) word = n2v_init_serial(p, cur, d, prev, dprev);
+        if (need && slot != kNoSlot) __stcg(p.memo + dprev.begin + slot, word);
+        if (step)
+        {
+            const float wn = class_weight(p, cls_new);                                       // sample :31-46
+            const float wo = class_weight(p, word >> 30);
+            bool acc = wo < wn;
+            if (!acc) acc = unit_double(keyed_draw(p.seed, kDomStep, walk_id, pos, 1)) <= (double) wn / (double) wo;
+            u32 next = cand;
+            if (!acc)
+            {
+                cslot = word & kSlotMask;
+                next = __ldg(p.pool + d.begin + cslot);
+                dcand = load_desc(p.desc, next);
+            }
+            __stcs(out, next);
+            prev = cur; dprev = d; cur = next; d = dcand; slot = cslot;
+            ++pos;
+            out += p.w_local;
+        }
+    }
+    u32 steps = 0;
+    if (owner)
+    {
+        // the draw at the last position is unobservable (:315-317) but counts as a step when the walker can move
+        steps = pos - first + ((!stopped && d.degree) ? 1u : 0u);
+        for (++pos; pos <= last_pos; ++pos, out += p.w_local) __stcs(out, kNoVertex);
+    }
+    block_add_u64(steps_out, steps);
+}
+
+// DeepWalk in MH mode: weight == 1 (deepwalk.h:67-70) so accept() is drand() <= 1.0, always true, and the walk
+// is the proposal chain (deepwalk.h:79-87) with keyed draws.
+template <bool kRewalk>
+__global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkParams p, const u32* __restrict__ affected,
+                                                                      const u32* __restrict__ positions, u64 count,
+                                                                      unsigned long long* steps_out)
 {
     const u64 t = (u64) blockIdx.x * kWalkBlock + threadIdx.x;
     u32 steps = 0;
     if (t < count)
     {
         u64 w;
-        u32 pos = 0, cur, prev;
+        u32 pos = 0, cur;
         if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = t; }
         const u32 replica = (u32) (w / p.n_local);
         const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
-        const u64 walk_id = (u64) replica * p.n + start;             // global id keys the draws
+        const u64 walk_id = (u64) replica * p.n + start;
         if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
         else { cur = start; p.walks[w] = cur; }
-        prev = cur;
-        if (kModel == WMH_NODE2VEC)
-        {
-            if (pos > 0) prev = p.walks[(u64) (pos - 1) * p.w_local + w];                 // wharfmh.h:819-823
-            else
-            {
-                const RowDesc d0 = load_desc(p.desc, cur);                                 // node2vec.h:42-49
-                if (d0.degree) prev = __ldg(p.pool + d0.begin + mod_u64_u32(keyed_draw(p.seed, kDomState, walk_id, 0, 0), d0.degree));
-            }
-        }
         u32* out = p.walks + (u64) (pos + 1) * p.w_local + w;
         const u32 first = pos;
         const u32 last_pos = p.L - 1;
-        bool stopped = false;
-        for (; pos < last_pos; ++pos, out += p.w_local)
+        RowDesc d = load_desc(p.desc, cur);
+        for (; pos < last_pos && d.degree; ++pos, out += p.w_local)
         {
-            const RowDesc d = load_desc(p.desc, cur);
-            if (d.degree == 0) { stopped = true; break; }
-            // propose_vertex - deepwalk.h:79-87 / node2vec.h:97-105
-            const u32 cand = __ldg(p.pool + d.begin + mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree));
-            u32 next;
-            if (kModel == WMH_DEEPWALK)
-            {
-                next = cand;               // weight == 1 (deepwalk.h:67-70): accept() is drand() <= 1.0, always true
-            }
-            else
-            {
-                const RowDesc dprev = load_desc(p.desc, prev);
-                // The sampler of state (cur, prev) lives in cur's SamplerManager (graph/vertex.h:12) and, because
-                // find() hands out copies (wharfmh.h:301,833), never advances past its init value: cache that
-                // value in the slot of edge cur->prev.  A re-written row starts with an empty cache, which is the
-                // reset of wharfmh.h:504->539.
-                u32 slot_index;
-                const bool has_slot = row_contains(p.pool, d, prev, &slot_index);
-                u32 last = kNoVertex;
-                if (has_slot) last = __ldcg(p.memo + d.begin + slot_index);
-                if (last == kNoVertex)
-                {
-                    last = n2v_sampler_init(p, cur, d, prev, dprev);
-                    if (has_slot) __stcg(p.memo + d.begin + slot_index, last);
-                }
-                const float wn = n2v_weight(p, prev, dprev, cand);                         // sample :31-46
-                const float wo = n2v_weight(p, prev, dprev, last);
-                bool acc = wo < wn;
-                if (!acc) acc = unit_double(keyed_draw(p.seed, kDomStep, walk_id, pos, 1)) <= (double) wn / (double) wo;
-                next = acc ? cand : last;
-            }
-            *out = next;
-            prev = cur;
-            cur = next;
+            cur = __ldg(p.pool + d.begin + mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree));
+            __stcs(out, cur);
+            d = load_desc(p.desc, cur);
         }
-        if (first == last_pos) stopped = load_desc(p.desc, cur).degree == 0;
-        steps = pos - first + (stopped ? 0u : 1u);
-        for (++pos; pos <= last_pos; ++pos, out += p.w_local) *out = kNoVertex;
+        steps = pos - first + (d.degree ? 1u : 0u);
+        for (++pos; pos <= last_pos; ++pos, out += p.w_local) __stcs(out, kNoVertex);
     }
     block_add_u64(steps_out, steps);
 }
@@ -461,9 +575,9 @@ void launch_walk(const LaunchCtx& lc, const WalkParams& wp, const u32* ids, cons
     if (wp.deterministic)
         walk_deterministic_kernel<kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
     else if (wp.model == WMH_NODE2VEC)
-        walk_mh_kernel<WMH_NODE2VEC, kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
+        walk_n2v_kernel<kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
     else
-        walk_mh_kernel<WMH_DEEPWALK, kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
+        walk_deepwalk_mh_kernel<kRewalk><<<grid, kWalkBlock, 0, lc.stream>>>(p, ids, positions, count, d_steps);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
 }

@@ -31,11 +31,12 @@ class Config:
     device: int = 0
     rank: int = 0
     world: int = 1
+    generate_mode: int = 0                # GENERATE_AUTO / GENERATE_PER_WALKER / GENERATE_COALESCED
 
     def to_c(self) -> WmhConfig:
         return WmhConfig(self.walks_per_vertex, self.walk_length, self.random_walk_model, int(self.deterministic_mode),
                          self.paramP, self.paramQ, self.sampler_init_strategy, self.search_mode, self.seed, self.device,
-                         self.rank, self.world, 0)
+                         self.rank, self.world, self.generate_mode)
 
 
 def _ptr(a):
@@ -291,6 +292,11 @@ class WharfMH:
 
     def synchronize(self) -> None:
         check(self._lib.wmh_synchronize(self._h))
+
+
+def trim_memory(device: int = 0) -> None:
+    """Returns the blocks cached by destroyed engines / finished batches to the driver (wmh_trim_memory)."""
+    check(capi.load().wmh_trim_memory(device))
 
 
 # ---- pairings (walks/pairings.h) over torch / raw device pointers ------------------------------------

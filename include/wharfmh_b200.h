@@ -60,6 +60,13 @@ typedef enum
     WMH_SEARCH_SCAN = 2       /* stream the walk matrix against the touched-vertex bitmap */
 } wmh_search_mode;
 
+typedef enum
+{
+    WMH_GENERATE_AUTO = 0,       /* coalesced when the adjacency does not fit the L2, one walker per thread otherwise */
+    WMH_GENERATE_PER_WALKER = 1, /* one walker per thread, two dependent random loads per step */
+    WMH_GENERATE_COALESCED = 2   /* step-synchronous: walkers of a replica that met are advanced once (deterministic mode only) */
+} wmh_generate_mode;
+
 /* The knobs of namespace config (config/globals.h:7-29) plus placement.  Read at call time, like the
  * reference reads its globals (graph/wharfmh.h:254-272). */
 typedef struct
@@ -76,7 +83,7 @@ typedef struct
     int32_t  device;             /* CUDA device ordinal */
     uint32_t rank;               /* shard of the walk corpus owned by this engine */
     uint32_t world;              /* number of shards (>= 1) */
-    uint32_t reserved;
+    uint32_t generate_mode;      /* wmh_generate_mode: how deterministic bulk generation is scheduled (same corpus either way) */
 } wmh_config;
 
 typedef struct wmh_engine wmh_engine;
@@ -235,6 +242,10 @@ WMH_API double   wmh_last_walk_kernel_ms(const wmh_engine* e);
 WMH_API const uint32_t* wmh_device_walks(const wmh_engine* e);
 WMH_API void*    wmh_stream(const wmh_engine* e);                        /* cudaStream_t */
 WMH_API int      wmh_synchronize(wmh_engine* e);
+/* Engines allocate stream-ordered from the device's default memory pool and leave freed blocks there for the next
+ * engine / batch (the analogue of the reference's static allocator pools, graph/wharfmh.h:1041-1047, which are
+ * never returned either).  This hands every unused block back to the driver. */
+WMH_API int      wmh_trim_memory(int device);
 
 /* ---- synthetic input (utils/utility.h:55-146 generate_batch_of_edges, rmat_util.h) --------------- */
 

@@ -397,3 +397,84 @@ def test_keyed_mh_mode_vs_oracle(wharf, wo, model, init):
     o2 = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=15, model=m, p=0.5, q=2.0, deterministic=False, init_strategy=ini, seed=78)
     o2.generate()
     assert not np.array_equal(o2.walks(), o.walks()) or True
+
+
+@pytest.mark.parametrize("init", ["weight", "random"])
+def test_keyed_mh_directed_batches_vs_oracle(wharf, wo, init):
+    """node2vec MH with DIRECTED insert/delete batches (no reverse edges): the sampler cache must stay equal to a
+    recomputation from the current graph, walkers may meet sinks, and prev may not be a neighbour of cur."""
+    rng = np.random.default_rng(5)
+    n = 1 << 8
+    off, adj = wo.rmat_graph(8, 1500, seed=4)
+    ini = {"weight": wo.INIT_WEIGHT, "random": wo.INIT_RANDOM}[init]
+    kw = dict(walks_per_vertex=5, walk_length=20)
+    o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.25, q=4.0, deterministic=False, init_strategy=ini, seed=3, **kw)
+    with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.25, paramQ=4.0, deterministic_mode=False,
+              sampler_init_strategy=ini, seed=3, **kw) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        assert np.array_equal(e.walks(), o.walks())
+        for step in range(8):
+            delete = step % 2 == 1
+            if delete:
+                row_ptr, col = o.csr()
+                pick = rng.integers(0, col.shape[0], 60)
+                src = np.searchsorted(row_ptr, pick, side="right") - 1
+                b = np.stack([src, col[pick]], 1).astype(np.uint32)            # one direction only
+            else:
+                b = random_batch(rng, n, 40, symmetric=False)
+            b = np.ascontiguousarray(b)
+            o.update(b, delete=delete, remove_dups=True)
+            (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
+            assert np.array_equal(e.affected_walks()[0], o.affected()[0])
+            assert e.last_steps() == o.steps_last()
+            assert np.array_equal(e.walks(), o.walks()), f"corpus differs after directed batch {step}"
+
+
+@pytest.mark.parametrize("case", ["rmat10", "rmat12_sparse", "directed_sinks", "short", "single"])
+def test_coalesced_generation_equals_oracle(wharf, wo, case):
+    """GENERATE_COALESCED (step-synchronous, walkers of a replica that met advance once) must give the corpus and
+    step count of the oracle and of the one-walker-per-thread kernel, including isolated starts, sinks of a
+    directed graph, walk_length 1/2 and sharded engines."""
+    wpv, L = 10, 80
+    if case == "rmat10":
+        n = 1 << 10
+        off, adj = wo.rmat_graph(10, 8000)
+    elif case == "rmat12_sparse":
+        n = 1 << 12
+        off, adj = wo.rmat_graph(12, 5000, seed=9)            # many isolated vertices
+    elif case == "directed_sinks":
+        n = 300
+        rng = np.random.default_rng(1)
+        pairs = np.unique(rng.integers(0, n, (900, 2)).astype(np.uint32), axis=0)
+        pairs = pairs[(pairs[:, 0] != pairs[:, 1]) & (pairs[:, 0] % 7 != 0)]     # every 7th vertex is a sink
+        off, adj = wo.csr_from_sorted_pairs(n, pairs)
+    elif case == "short":
+        n, wpv, L = 1 << 9, 3, 2
+        off, adj = wo.rmat_graph(9, 3000)
+    else:
+        n, wpv, L = 1 << 9, 1, 1
+        off, adj = wo.rmat_graph(9, 3000)
+    o = wo.Oracle(n, off, adj, walks_per_vertex=wpv, walk_length=L)
+    steps = o.generate()
+    with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=L, generate_mode=wharf.GENERATE_COALESCED) as e:
+        assert e.generate_initial_random_walks() == steps
+        assert np.array_equal(e.walks(), o.walks())
+        # and a batch afterwards re-walks from the coalesced corpus exactly like the oracle
+        b = wo.generate_batch(20, n, 1, False, False)
+        o.update(b, delete=False, remove_dups=True)
+        e.insert_edges_batch(b.copy(), remove_dups=True)
+        assert np.array_equal(e.walks(), o.walks())
+    with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=L, generate_mode=wharf.GENERATE_PER_WALKER) as e:
+        assert e.generate_initial_random_walks() == steps
+    o2 = wo.Oracle(n, off, adj, walks_per_vertex=wpv, walk_length=L)
+    o2.generate()
+    for world in (2, 3):
+        full = np.empty_like(o2.walks())
+        total = 0
+        for r in range(world):
+            with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=L, rank=r, world=world,
+                      generate_mode=wharf.GENERATE_COALESCED) as e:
+                total += e.generate_initial_random_walks()
+                full[e.local_walk_ids().astype(np.int64)] = e.walks()
+        assert total == steps
+        assert np.array_equal(full, o2.walks())

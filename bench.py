@@ -350,9 +350,7 @@ def main():
             t = [time.perf_counter()]
             eng = wharf.WharfMH(n, m, h_off.numpy().view(np.uint64), h_adj.numpy().view(np.uint32), config=cfg)   # H2D
             t.append(time.perf_counter())
-            s = eng.generate_initial_random_walks()
-            t.append(time.perf_counter())
-            wharf._capi.check(lib.wmh_walks_copy(eng._h, 0, w_count, C.c_void_p(h_walks_np.ctypes.data)))        # D2H
+            s = eng.generate_initial_random_walks_to_host(h_walks_np)                                             # generate + D2H, overlapped
             t.append(time.perf_counter())
             eng.destroy()
             t.append(time.perf_counter())
@@ -371,8 +369,8 @@ def main():
         e2e = {"value": sum_over_ranks(e_steps) / e2e_s, "unit": "walk-steps/s",
                "h2d_bytes_per_step": int(n * 8 + m * 4), "d2h_bytes_per_step": int(w_count * LEN * 4),
                "iters": e2e_iters, "ms_per_step": 1e3 * e2e_s / e2e_iters,
-               "phases_ms_last": dict(zip(("create_h2d", "generate", "walks_copy_d2h", "destroy"), e2e_phases[-1])),
-               "path": "wmh_create(host CSR) + wmh_generate_initial_random_walks + wmh_walks_copy(pinned host), per rank"}
+               "phases_ms_last": dict(zip(("create_h2d", "generate_to_host", "destroy"), e2e_phases[-1])),
+               "path": "wmh_create(host CSR) + wmh_generate_initial_random_walks_to_host(pinned host: whole corpus D2H overlapped with the walk kernels) + wmh_destroy, per rank"}
         engine = wharf.WharfMH(n, m, d_offsets.data_ptr(), d_edges.data_ptr(), config=cfg, device_arrays=True)
 
     # ---- edge-batch update latency (second half of BASELINE.json's metric) ----

@@ -72,6 +72,7 @@ SIGNATURES = {
     "wmh_degree": (i32, [vp, u32, PU64]),
     "wmh_neighbors": (i32, [vp, u32, vp, u64, PU64]),
     "wmh_generate_initial_random_walks": (i32, [vp]),
+    "wmh_generate_initial_random_walks_to_host": (i32, [vp, vp, u64]),
     "wmh_last_steps": (u64, [vp]),
     "wmh_number_of_walks": (u64, [vp]),
     "wmh_number_of_local_walks": (u64, [vp]),

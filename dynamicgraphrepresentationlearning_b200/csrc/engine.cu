@@ -53,6 +53,7 @@ struct wmh_engine
 {
     wmh_config cfg{};
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // corpus export overlapped with generation (generate_and_export)
     int sm_count = 148;
     u64 launches = 0, library_calls = 0;
 
@@ -97,6 +98,7 @@ struct wmh_engine
     {
         cudaSetDevice(cfg.device);
         if (stream) cudaStreamSynchronize(stream);
+        if (copy_stream) { cudaStreamSynchronize(copy_stream); cudaStreamDestroy(copy_stream); }
         for (auto& e : ev) if (e) cudaEventDestroy(e);
         // buffers release in their destructors; the stream goes last
     }
@@ -128,13 +130,16 @@ std::unique_ptr<wmh_engine> make_engine(const wmh_config* cfg)
         throw CudaError(e == cudaSuccess ? cudaErrorNoDevice : e, "no CUDA device available: libwharfmh_b200 has no CPU path");
     }
     if (cfg->device < 0 || cfg->device >= count) throw std::invalid_argument("device ordinal out of range");
+    Trace tr(nullptr);
     auto eng = std::make_unique<wmh_engine>();
     eng->cfg = *cfg;
     eng->bind();
-    cudaDeviceProp prop{};
-    WHARF_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
-    if (prop.major < 10) throw CudaError(cudaErrorInvalidDevice, std::string("device '") + prop.name + "' is not sm_100-class; this library carries sm_100a code only");
-    eng->sm_count = prop.multiProcessorCount;
+    int major = 0, sms = 0;                 // attribute queries: cudaGetDeviceProperties costs ~3 ms per call
+    WHARF_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, cfg->device));
+    WHARF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device));
+    if (major < 10) throw CudaError(cudaErrorInvalidDevice, "device " + std::to_string(cfg->device) + " is not sm_100-class; this library carries sm_100a code only");
+    eng->sm_count = sms;
+    tr.mark("create: device properties");
     // Random 32-byte sector gathers dominate this path: stop L2 from widening every miss into a larger DRAM fetch
     // (measured on B200: 86 B of DRAM traffic per 32 B request at the default granularity; profiles/r01b_*).
     {
@@ -143,6 +148,7 @@ std::unique_ptr<wmh_engine> make_engine(const wmh_config* cfg)
         if (granularity) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, granularity);
         cudaGetLastError();
     }
+    tr.mark("create: L2 fetch limit");
     WHARF_CUDA(cudaStreamCreateWithFlags(&eng->stream, cudaStreamNonBlocking));
     eng->bind();
     for (auto& ev : eng->ev) WHARF_CUDA(cudaEventCreate(&ev));
@@ -153,6 +159,7 @@ std::unique_ptr<wmh_engine> make_engine(const wmh_config* cfg)
     WHARF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
     eng->d_steps.allocate(1);
     eng->small.allocate(16);
+    tr.mark("create: stream+events+pool");
     return eng;
 }
 
@@ -162,6 +169,7 @@ void finish_graph(wmh_engine& e, u64 n, u64 m, const u64* d_offsets, const u32* 
     if (n >= 0xFFFFFFFEull) throw std::invalid_argument("vertex ids must fit 32 bits");
     if (m >= (1ull << 32)) throw std::invalid_argument("more than 2^32 directed edges are not supported by the u32 row descriptors");
     auto lc = e.lc();
+    Trace tr(e.stream);
     e.g.n = n;
     e.g.m = m;
     e.g.desc.allocate(n);
@@ -176,9 +184,12 @@ void finish_graph(wmh_engine& e, u64 n, u64 m, const u64* d_offsets, const u32* 
     e.g.pool_used = m;
     e.bitmap.allocate((n + 31) / 32);
     WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    tr.mark("create: graph buffers+copy");
 }
 
 u32 local_starts(u64 n, u32 rank, u32 world) { return rank < n ? (u32) ((n - rank + world - 1) / world) : 0; }
+
+u64 local_walk_capacity(const wmh_engine* e) { return (u64) local_starts(e->g.n, e->cfg.rank, e->cfg.world) * e->cfg.walks_per_vertex; }
 
 WalkParams walk_params(wmh_engine& e)
 {
@@ -186,7 +197,7 @@ WalkParams walk_params(wmh_engine& e)
     wp.desc = e.g.desc.ptr;
     wp.pool = e.g.pool.ptr;
     wp.version = e.g.version.ptr;
-    wp.memo = e.g.memo.ptr;
+    wp.pool_rw = e.g.tail ? e.g.pool.ptr : nullptr;
     wp.draw = e.draw.ptr;
     wp.walks = e.walks.ptr;
     wp.n = e.g.n;
@@ -207,14 +218,13 @@ WalkParams walk_params(wmh_engine& e)
 
 bool needs_memo(const wmh_engine& e) { return !e.cfg.deterministic && e.cfg.model == WMH_NODE2VEC; }
 
-void ensure_memo(wmh_engine& e)
+// MH node2vec keeps its sampler caches and neighbour filter in aux tails behind the rows (kernels_graph.cu): switch
+// the pool to that layout the first time it is needed.
+void ensure_tails(wmh_engine& e)
 {
-    if (!needs_memo(e)) return;
-    if (e.g.memo.count != e.g.pool.count)
-    {
-        e.g.memo.allocate(e.g.pool.count);
-        WHARF_CUDA(cudaMemsetAsync(e.g.memo.ptr, 0xFF, e.g.memo.bytes(), e.stream));
-    }
+    if (!needs_memo(e) || e.g.tail) return;
+    auto lc = e.lc();
+    graph_enable_tails(lc, e.g);
 }
 
 // Deterministic bulk generation: the coalesced schedule pays ~6 small launches per position, the per-walker kernel
@@ -226,7 +236,63 @@ bool use_coalesced(const wmh_engine& e)
     return e.g.n * sizeof(RowDesc) + e.g.m * sizeof(u32) > (96ull << 20);
 }
 
-void generate(wmh_engine& e)
+// Bulk generation with the corpus streamed to the host while it is produced: the walkers are generated in
+// ranges (replica by replica on the coalesced schedule); as soon as a range is complete the copy stream
+// transposes it to walk-major rows in a staging buffer and copies it out, overlapping the next range's kernel
+// with the PCIe transfer.  Same corpus and step count as generate() + wmh_walks_copy.
+void generate_and_export(wmh_engine& e, u32* host_out)
+{
+    auto lc = e.lc();
+    const u32 L = e.walks_L;
+    if (!e.copy_stream)
+    {
+        // highest priority: the transposes must get SM slots while the next range's walk kernel fills the machine
+        int least = 0, greatest = 0;
+        WHARF_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        WHARF_CUDA(cudaStreamCreateWithPriority(&e.copy_stream, cudaStreamNonBlocking, greatest));
+    }
+    LaunchCtx copy_lc{e.copy_stream, e.sm_count, &e.launches, &e.library_calls};
+    const u64 max_stage_walks = std::max<u64>(256, (128ull << 20) / L);                 // 512 MiB of staging at most
+    u64 piece = std::min(max_stage_walks, std::max<u64>(256, (e.w_local + 7) / 8));
+    piece = (piece + 255) / 256 * 256;
+    Scratch<u32> stage(e.copy_stream, piece * L);
+    std::vector<cudaEvent_t> events;
+    auto export_range = [&](u64 first, u64 count) {                                      // [first, first + count) is complete on e.stream
+        cudaEvent_t ev;
+        WHARF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        events.push_back(ev);
+        WHARF_CUDA(cudaEventRecord(ev, e.stream));
+        WHARF_CUDA(cudaStreamWaitEvent(e.copy_stream, ev, 0));
+        for (u64 done = 0; done < count; done += piece)
+        {
+            const u64 c = std::min(piece, count - done);
+            walks_transpose_rows(copy_lc, e.walks.ptr, e.w_local, L, first + done, c, stage.ptr);
+            WHARF_CUDA(cudaMemcpyAsync(host_out + (first + done) * L, stage.ptr, c * L * sizeof(u32), cudaMemcpyDeviceToHost, e.copy_stream));
+        }
+    };
+    const WalkParams wp = walk_params(e);
+    if (use_coalesced(e))
+    {
+        const u64 nl = e.n_local;
+        walks_generate_coalesced(lc, wp, e.host_draw.data(), e.d_steps.ptr, [&](u32 replica) { export_range((u64) replica * nl, nl); });
+    }
+    else
+    {
+        // generation ranges: an eighth of the corpus each (a range is several full waves of walker blocks; its copy
+        // starts when its kernel ends), copied out in staging-sized pieces
+        const u64 range = std::max(piece, ((e.w_local + 7) / 8 + 255) / 256 * 256);
+        for (u64 first = 0; first < e.w_local; first += range)
+        {
+            const u64 c = std::min(range, e.w_local - first);
+            walks_generate_range(lc, wp, first, c, e.d_steps.ptr);
+            export_range(first, c);
+        }
+    }
+    WHARF_CUDA(cudaStreamSynchronize(e.copy_stream));
+    for (cudaEvent_t ev : events) cudaEventDestroy(ev);
+}
+
+void generate(wmh_engine& e, u32* host_out = nullptr)
 {
     e.bind();
     validate_config(e.cfg);
@@ -241,8 +307,10 @@ void generate(wmh_engine& e)
     e.index.valid = false;
     e.codes_valid = false;
     e.n_affected = 0;
+    Trace tr(e.stream);
     e.walks.ensure(std::max<u64>(1, e.w_local * L));
     e.min_pos.ensure(std::max<u64>(1, e.w_local));
+    tr.mark("generate: corpus buffers");
     if (e.draw_wpv != wpv || e.draw_len != L)
     {
         e.host_draw = make_draw_table(wpv, L);
@@ -255,23 +323,27 @@ void generate(wmh_engine& e)
     }
     if (needs_memo(e))
     {
-        e.g.memo.release();          // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90)
-        ensure_memo(e);
+        if (e.g.tail) graph_aux_clear_caches(lc, e.g);   // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90)
+        else ensure_tails(e);
     }
+    tr.mark("generate: draws+memo+filter");
     WHARF_CUDA(cudaMemsetAsync(e.d_steps.ptr, 0, 8, e.stream));
     WHARF_CUDA(cudaEventRecord(e.ev[0], e.stream));
-    if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr);
+    if (host_out) generate_and_export(e, host_out);
+    else if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr, nullptr);
     else walks_generate(lc, walk_params(e), e.d_steps.ptr);
     WHARF_CUDA(cudaEventRecord(e.ev[1], e.stream));
     unsigned long long steps = 0;
     WHARF_CUDA(cudaMemcpyAsync(&steps, e.d_steps.ptr, 8, cudaMemcpyDeviceToHost, e.stream));
     WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    if (host_out) WHARF_CUDA(cudaStreamSynchronize(e.copy_stream));
     float ms = 0;
     WHARF_CUDA(cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]));
     e.last_walk_kernel_ms = ms;
     e.timers[WMH_TIMER_GENERATE] = ms * 1e-3;
     e.last_steps = steps;
     e.have_walks = true;
+    tr.mark("generate: walk (+export)");
     if (e.cfg.search_mode == WMH_SEARCH_INDEX) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
 }
 
@@ -297,7 +369,7 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
     PreparedBatch batch;
     graph_prepare_batch(lc, d_pairs, count, remove_dups, e.g.n, batch, d_sorted_out);
     WHARF_CUDA(cudaMemsetAsync(e.bitmap.ptr, 0, e.bitmap.bytes(), e.stream));
-    if (needs_memo(e) && e.have_walks) ensure_memo(e);
+    if (needs_memo(e) && e.have_walks) ensure_tails(e);
     graph_apply_batch(lc, e.g, batch, is_delete, e.bitmap.ptr);
     e.codes_valid = false;
     e.n_touched = batch.n_sources;
@@ -653,6 +725,16 @@ int wmh_generate_initial_random_walks(wmh_engine* e)
     });
 }
 
+int wmh_generate_initial_random_walks_to_host(wmh_engine* e, uint32_t* out, uint64_t capacity_walks)
+{
+    if (!e || !out) return fail(WMH_ERR_INVALID, "null argument");
+    if (capacity_walks < local_walk_capacity(e)) return fail(WMH_ERR_RANGE, "corpus buffer too small");
+    return guarded([&] {
+        generate(*e, out);
+        return (int) WMH_OK;
+    });
+}
+
 uint64_t wmh_last_steps(const wmh_engine* e) { return e ? e->last_steps : 0; }
 uint64_t wmh_number_of_walks(const wmh_engine* e) { return e ? e->g.n * (e->have_walks ? e->walks_wpv : e->cfg.walks_per_vertex) : 0; }
 uint64_t wmh_number_of_local_walks(const wmh_engine* e)
@@ -974,7 +1056,7 @@ int wmh_memory_footprint(wmh_engine* e, wmh_memory* out)
     if (!e || !out) return fail(WMH_ERR_INVALID, "null argument");
     std::memset(out, 0, sizeof(*out));
     out->graph_bytes = e->g.desc.bytes() + e->g.m * sizeof(u32) + e->g.version.bytes();
-    out->graph_pool_bytes = e->g.pool.bytes() + e->g.memo.bytes();
+    out->graph_pool_bytes = e->g.pool.bytes() + e->g.spare.bytes();
     out->walks_bytes = e->have_walks ? e->w_local * e->walks_L * sizeof(u32) : 0;
     out->index_bytes = e->index.valid ? e->index.ptr.bytes() + e->index.entries * sizeof(u32) + (e->codes_valid ? e->codes.bytes() : 0) : 0;
     out->scratch_bytes = e->min_pos.bytes() + e->aff_ids.bytes() + e->aff_pos.bytes() + e->bitmap.bytes() + e->touched.bytes() + e->draw.bytes();

@@ -4,6 +4,10 @@
 #include "common.cuh"
 #include "../../include/wharfmh_b200.h"
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
 #include <vector>
 
 namespace wharf
@@ -16,6 +20,28 @@ struct LaunchCtx
     u64* library_calls = nullptr; // CUB device-wide algorithm invocations
     void count(u64 k = 1) const { if (launches) *launches += k; }
     void count_lib(u64 k = 1) const { if (library_calls) *library_calls += k; }
+};
+
+// WHARF_TRACE=1: host-timed phases with the stream synchronised at every mark; WHARF_TRACE=2: host time between
+// marks without synchronising (shows where the submitting thread blocks).  Tuning aid only, stderr.
+struct Trace
+{
+    cudaStream_t stream;
+    int mode;
+    std::chrono::steady_clock::time_point t0;
+    explicit Trace(cudaStream_t s) : stream(s), mode(std::getenv("WHARF_TRACE") ? std::atoi(std::getenv("WHARF_TRACE")) : 0)
+    {
+        if (mode == 1) cudaStreamSynchronize(s);
+        if (mode) t0 = std::chrono::steady_clock::now();
+    }
+    void mark(const char* what)
+    {
+        if (!mode) return;
+        if (mode == 1) cudaStreamSynchronize(stream);
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[wharf trace] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
 };
 
 // Stream-ordered scratch allocation (cudaMallocAsync), released at scope exit.
@@ -64,10 +90,11 @@ struct DeviceGraph
     u64 n = 0;                       // number_of_vertices()
     u64 m = 0;                       // number_of_edges() (directed entries)
     DeviceBuffer<RowDesc> desc;      // n
-    DeviceBuffer<u32> pool;          // neighbour pool, rows ascending & unique
-    u64 pool_used = 0;               // elements of pool handed out (live + garbage)
+    DeviceBuffer<u32> pool;          // neighbour pool, rows ascending & unique (+ aux tails, see `tail`)
+    u64 pool_used = 0;               // words of pool handed out (live + garbage)
     DeviceBuffer<u32> version;       // n: sampler-manager generation per vertex (graph/vertex.h:12)
-    DeviceBuffer<u32> memo;          // optional, aligned with pool: cached sampler init value per edge cur->prev
+    DeviceBuffer<u32> spare;         // second pool: compaction copies into it and swaps (no allocation in steady state)
+    u32 tail = 0;                    // 1: every row is followed by `degree` aux words (sampler cache | neighbour filter), MH node2vec
 };
 
 // One prepared edge batch (sorted, deduplicated) and what the merge learned about it.
@@ -87,6 +114,11 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
 // Applies the batch; returns the pool elements appended. Updates g.m, g.pool_used, version[], touched bitmap.
 void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch& b, bool is_delete, u32* d_touched_bitmap);
 void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity);
+// Aux tails (MH node2vec): switch the layout on (one compaction), rebuild every tail (filter set, caches empty), or
+// only empty the sampler caches.
+void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g);
+void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g);
+void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g);
 void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr /* n+1 */, u32* d_col /* m */);
 void graph_check_ids(const LaunchCtx& lc, const u32* d_pairs, u64 count, u64 n, u32* d_flag);
 void rmat_generate_device(const LaunchCtx& lc, u64 edges_number, u64 vertices_number, u64 batch_seed, bool self_loops,
@@ -99,7 +131,7 @@ struct WalkParams
     const RowDesc* desc = nullptr;
     const u32* pool = nullptr;
     const u32* version = nullptr;
-    u32* memo = nullptr;             // sampler-state cache aligned with pool (MH node2vec), kNoVertex = empty
+    u32* pool_rw = nullptr;          // the same pool, writable: aux tails (MH node2vec; DeviceGraph::tail must be 1)
     const u64* draw = nullptr;       // X[wpv][L]
     u32* walks = nullptr;            // [L][W_local] position-major
     u64 n = 0;                       // global vertices
@@ -116,7 +148,12 @@ void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affect
                   unsigned long long* d_steps);
 // Deterministic mode only: step-synchronous generation that advances walkers standing on the same vertex once
 // (kernels_coalesced.cu).  host_draw = X[wpv][L] on the host.
-void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps);
+// after_replica(r), when given, is called once replica r's column block [r * n_local, (r + 1) * n_local) has been
+// fully enqueued on lc.stream.
+void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
+                              const std::function<void(u32)>& after_replica);
+// Bulk generation of the local walks [first, first + count) with one walker per thread.
+void walks_generate_range(const LaunchCtx& lc, const WalkParams& wp, u64 first, u64 count, unsigned long long* d_steps);
 // min_pos[w] = first position whose vertex is in the touched bitmap (kNoPos when none).
 void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_bitmap, u32* d_min_pos);
 // Compacts min_pos != kNoPos into (ids, positions); returns the count.

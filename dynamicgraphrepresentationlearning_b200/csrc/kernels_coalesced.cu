@@ -197,7 +197,8 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, const u32* cv, u32*
 }
 }  // namespace
 
-void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps)
+void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
+                              const std::function<void(u32)>& after_replica)
 {
     if (wp.w_local == 0) return;
     const u32 nl = wp.n_local, L = wp.L;
@@ -242,6 +243,7 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
             a += k;
         }
         WHARF_CUDA(cudaGetLastError());
+        if (after_replica) after_replica(r);
     }
 }
 

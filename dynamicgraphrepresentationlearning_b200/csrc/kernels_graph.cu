@@ -22,28 +22,6 @@
 
 namespace wharf
 {
-// WHARF_TRACE=1: host-timed phases with the stream synchronised at every mark; WHARF_TRACE=2: host time between
-// marks without synchronising (shows where the submitting thread blocks).  Tuning aid only, stderr.
-struct Trace
-{
-    cudaStream_t stream;
-    int mode;
-    std::chrono::steady_clock::time_point t0;
-    explicit Trace(cudaStream_t s) : stream(s), mode(std::getenv("WHARF_TRACE") ? std::atoi(std::getenv("WHARF_TRACE")) : 0)
-    {
-        if (mode == 1) cudaStreamSynchronize(s);
-        if (mode) t0 = std::chrono::steady_clock::now();
-    }
-    void mark(const char* what)
-    {
-        if (!mode) return;
-        if (mode == 1) cudaStreamSynchronize(stream);
-        const auto t1 = std::chrono::steady_clock::now();
-        std::fprintf(stderr, "[wharf trace] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
-        t0 = t1;
-    }
-};
-
 namespace
 {
 constexpr u32 kChunk = 1024;      // old-row elements copied by one warp in the merge
@@ -125,15 +103,16 @@ __global__ void locate_kernel(const u64* __restrict__ keys, u64 k, const RowDesc
 
 // Per source: new degree, merge chunks of the old row.
 __global__ void plan_rows_kernel(const u32* __restrict__ sources, const u64* __restrict__ slice, u64 n_sources,
-                                 const u64* __restrict__ change_scan, const RowDesc* __restrict__ desc, bool is_delete,
-                                 u64* __restrict__ new_degree, u64* __restrict__ chunks)
+                                 const u64* __restrict__ change_scan, const RowDesc* __restrict__ desc, bool is_delete, u32 row_words,
+                                 u64* __restrict__ new_degree, u64* __restrict__ alloc, u64* __restrict__ chunks)
 {
     const u64 j = (u64) blockIdx.x * blockDim.x + threadIdx.x;
     if (j > n_sources) return;
-    if (j == n_sources) { new_degree[j] = 0; chunks[j] = 0; return; }
+    if (j == n_sources) { new_degree[j] = 0; alloc[j] = 0; chunks[j] = 0; return; }
     const u32 old_deg = desc[sources[j]].degree;
     const u64 delta = change_scan[slice[j + 1]] - change_scan[slice[j]];
     new_degree[j] = is_delete ? old_deg - delta : old_deg + delta;
+    alloc[j] = new_degree[j] * row_words;                       // neighbours (+ the aux tail of the same length)
     chunks[j] = (old_deg + kChunk - 1) / kChunk;
 }
 
@@ -205,26 +184,71 @@ __global__ void commit_rows_kernel(const u32* __restrict__ sources, u64 n_source
     if (bitmap) atomicOr(bitmap + (v >> 5), 1u << (v & 31));
 }
 
-// The sampler cache word of state (cur, prev) sits in the slot of cur in the row of prev (kernels_walk.cu) and is a
-// function of the rows of cur and prev and of version[cur].  Rows re-written by the batch start with an empty
-// cache; this pass empties every other word whose cur is a batch source (bit set in the touched bitmap).  One
-// streaming pass over the used part of the pool: it needs no reverse adjacency, so it is exact for directed graphs.
-__global__ void __launch_bounds__(256) invalidate_memo_stream_kernel(const u32* __restrict__ pool, u64 used, const u32* __restrict__ bitmap,
-                                                                     u32* __restrict__ memo)
+// ---- aux tails (MH node2vec) ----------------------------------------------------------------------------
+// With g.tail a row of degree d owns 2 d pool words: d ascending neighbours, then d aux words.  Aux word i:
+//   low 16 bits   sampler cache of the state (cur = neighbour i, prev = this row's vertex)   (kernels_walk.cu)
+//   high 16 bits  block i of the row's neighbour filter                                        (common.cuh)
+// so everything a walker in state (cur, prev) needs from prev - cache word, filter block, the row itself - sits in
+// one short run of memory, next to the words its previous step already touched.
+
+// One warp per row: zero the tail, then set the filter bits of every neighbour.
+__device__ __forceinline__ void aux_build_row(u32* __restrict__ pool, u32 begin, u32 degree, u32 lane)
 {
-    for (u64 e = (u64) blockIdx.x * 256 + threadIdx.x; e < used; e += (u64) gridDim.x * 256)
+    u32* tail = pool + begin + degree;
+    for (u32 i = lane; i < degree; i += 32) tail[i] = 0;
+    __syncwarp();
+    for (u32 i = lane; i < degree; i += 32)
     {
-        const u32 c = __ldcs(pool + e);
-        if ((__ldg(bitmap + (c >> 5)) >> (c & 31)) & 1u) memo[e] = 0xFFFFFFFFu;
+        const u32 h = filter_hash(pool[begin + i]);
+        atomicOr(tail + filter_block(h, degree), filter_bits(h) << 16);
+    }
+}
+
+__global__ void __launch_bounds__(256) aux_build_all_kernel(const RowDesc* __restrict__ desc, u64 n, u32* __restrict__ pool)
+{
+    const u64 v = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (v >= n) return;
+    const uint2 d = reinterpret_cast<const uint2*>(desc)[v];
+    aux_build_row(pool, d.x, d.y, threadIdx.x & 31);
+}
+
+__global__ void __launch_bounds__(256) aux_build_sources_kernel(const u32* __restrict__ sources, u64 n_sources, const RowDesc* __restrict__ desc,
+                                                                u32* __restrict__ pool)
+{
+    const u64 j = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (j >= n_sources) return;
+    const uint2 d = reinterpret_cast<const uint2*>(desc)[sources[j]];
+    aux_build_row(pool, d.x, d.y, threadIdx.x & 31);
+}
+
+// The cache half of aux word i of row p is a function of the rows of cur = neighbour i and of p and of version[cur].
+// Rows re-written by a batch get a fresh (empty) tail; this pass empties every other cache whose cur is a batch
+// source (bit set in the touched bitmap).  One warp per row over all rows: no reverse adjacency needed, so it is
+// exact for directed graphs.  bitmap == nullptr empties every cache (a fresh corpus, wharfmh.h:41,83,90).
+__global__ void __launch_bounds__(256) aux_invalidate_kernel(const RowDesc* __restrict__ desc, u64 n, u32* __restrict__ pool, const u32* __restrict__ bitmap)
+{
+    const u64 v = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (v >= n) return;
+    const uint2 d = reinterpret_cast<const uint2*>(desc)[v];
+    unsigned short* cache = reinterpret_cast<unsigned short*>(pool + d.x + d.y);      // low half of aux word i = cache[2 i]
+    for (u32 i = threadIdx.x & 31; i < d.y; i += 32)
+    {
+        bool clear = true;
+        if (bitmap)
+        {
+            const u32 c = pool[d.x + i];
+            clear = (__ldg(bitmap + (c >> 5)) >> (c & 31)) & 1u;
+        }
+        if (clear) cache[2 * i] = 0;
     }
 }
 
 // ---- row copy (compaction / export) ---------------------------------------------------------------
-__global__ void degrees_kernel(const RowDesc* __restrict__ desc, u64 n, u64* __restrict__ deg)
+__global__ void degrees_kernel(const RowDesc* __restrict__ desc, u64 n, u32 row_words, u64* __restrict__ deg)
 {
     const u64 v = (u64) blockIdx.x * blockDim.x + threadIdx.x;
     if (v > n) return;
-    deg[v] = v < n ? desc[v].degree : 0;
+    deg[v] = v < n ? (u64) desc[v].degree * row_words : 0;
 }
 
 // 8 lanes per row; rows above kBigRow are left to copy_big_rows_kernel.
@@ -458,38 +482,59 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
     WHARF_CUDA(cudaGetLastError());
 }
 
+// Rewrites every live row contiguously in vertex order (in the layout g.tail asks for) into the spare pool and
+// swaps the two: garbage left by earlier batches is reclaimed, and a layout change (tail 0 -> 1) is the same copy.
+// The spare is kept, so steady-state compaction allocates nothing.  Aux tails come out rebuilt: filter set,
+// caches empty (the cache holds pure functions of (graph, key): dropping it is always safe).
 void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity)
 {
-    // new pool sized for the live edges, the pending append and half as much again of slack
-    u64 capacity = g.m + extra_capacity;
-    capacity += capacity / 2 + (1u << 20);
+    const u64 row_words = 1 + g.tail;
+    const u64 live = g.m * row_words;
+    u64 capacity = live + extra_capacity;
+    capacity += capacity / 2 + (1u << 20);                       // half as much again of slack
     if (capacity >= (1ull << 32)) capacity = (1ull << 32) - 1;
-    if (g.m + extra_capacity > capacity) throw CudaError(cudaErrorMemoryAllocation, "neighbour pool would exceed 2^32 entries");
+    if (live + extra_capacity > capacity) throw CudaError(cudaErrorMemoryAllocation, "neighbour pool would exceed 2^32 words");
     Trace tr(lc.stream);
     Scratch<u64> deg(lc.stream, g.n + 1), begin(lc.stream, g.n + 1);
-    degrees_kernel<<<div_up(g.n + 1, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, deg.ptr);
+    degrees_kernel<<<div_up(g.n + 1, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, (u32) row_words, deg.ptr);
     lc.count();
     exclusive_sum(lc, deg.ptr, begin.ptr, g.n + 1);
     tr.mark("compact: degrees+scan");
-    DeviceBuffer<u32> fresh;
-    fresh.allocate(capacity);
-    tr.mark("compact: cudaMalloc pool");
-    copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, begin.ptr, fresh.ptr);
+    if (g.spare.count < capacity) g.spare.allocate(capacity);
+    tr.mark("compact: spare pool");
+    copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, begin.ptr, g.spare.ptr);
     tr.mark("compact: copy_all_rows");
     repoint_kernel<<<div_up(g.n, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, begin.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
+    std::swap(g.pool, g.spare);
+    g.pool_used = live;
+    if (g.tail) graph_aux_rebuild(lc, g);
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
-    g.pool = std::move(fresh);
-    g.pool_used = g.m;
-    tr.mark("compact: repoint+free old");
-    if (g.memo.ptr)
-    {
-        // the cache holds pure functions of (graph, key): dropping it is always safe
-        g.memo.allocate(capacity);
-        WHARF_CUDA(cudaMemsetAsync(g.memo.ptr, 0xFF, capacity * sizeof(u32), lc.stream));
-        tr.mark("compact: memo realloc");
-    }
+    tr.mark("compact: repoint+aux");
+}
+
+void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g)
+{
+    if (!g.tail || g.n == 0) return;
+    aux_build_all_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g)
+{
+    if (!g.tail || g.n == 0) return;
+    aux_invalidate_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr, nullptr);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g)
+{
+    if (g.tail) return;
+    g.tail = 1;
+    graph_compact(lc, g, 0);
 }
 
 void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch& b, bool is_delete, u32* d_touched_bitmap)
@@ -504,15 +549,15 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     WHARF_CUDA(cudaGetLastError());
     exclusive_sum(lc, change.ptr, change_scan.ptr, k + 1);
 
-    Scratch<u64> new_degree(lc.stream, ns + 1), chunks(lc.stream, ns + 1), alloc_scan(lc.stream, ns + 1), chunk_scan(lc.stream, ns + 1);
-    plan_rows_kernel<<<div_up(ns + 1, 256), 256, 0, lc.stream>>>(b.sources.ptr, b.slice.ptr, ns, change_scan.ptr, g.desc.ptr, is_delete,
-                                                                 new_degree.ptr, chunks.ptr);
+    Scratch<u64> new_degree(lc.stream, ns + 1), alloc(lc.stream, ns + 1), chunks(lc.stream, ns + 1), alloc_scan(lc.stream, ns + 1), chunk_scan(lc.stream, ns + 1);
+    plan_rows_kernel<<<div_up(ns + 1, 256), 256, 0, lc.stream>>>(b.sources.ptr, b.slice.ptr, ns, change_scan.ptr, g.desc.ptr, is_delete, 1 + g.tail,
+                                                                 new_degree.ptr, alloc.ptr, chunks.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
-    exclusive_sum(lc, new_degree.ptr, alloc_scan.ptr, ns + 1);
+    exclusive_sum(lc, alloc.ptr, alloc_scan.ptr, ns + 1);
     exclusive_sum(lc, chunks.ptr, chunk_scan.ptr, ns + 1);
 
-    u64 totals[3];   // appended elements, chunks, changed edges
+    u64 totals[3];   // appended pool words, chunks, changed edges
     WHARF_CUDA(cudaMemcpyAsync(&totals[0], alloc_scan.ptr + ns, 8, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaMemcpyAsync(&totals[1], chunk_scan.ptr + ns, 8, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaMemcpyAsync(&totals[2], change_scan.ptr + k, 8, cudaMemcpyDeviceToHost, lc.stream));
@@ -520,7 +565,8 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     const u64 total = totals[0], n_chunks = totals[1], changed = totals[2];
     tr.mark("apply: locate+plan");
 
-    if (g.pool_used + total > g.pool.count) graph_compact(lc, g, total);    // rank[] is row-relative: still valid
+    const bool compacted = g.pool_used + total > g.pool.count;
+    if (compacted) graph_compact(lc, g, total);                            // rank[] is row-relative: still valid
     const u64 base = g.pool_used;
     tr.mark("apply: compact (if any)");
 
@@ -542,26 +588,23 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     lc.count();
     WHARF_CUDA(cudaGetLastError());
     tr.mark("apply: merge+write+commit");
-    if (g.memo.ptr)
-    {
-        if (total) WHARF_CUDA(cudaMemsetAsync(g.memo.ptr + base, 0xFF, total * sizeof(u32), lc.stream));   // fresh rows: empty cache
-        if (d_touched_bitmap && base)
-        {
-            invalidate_memo_stream_kernel<<<grid_for(base, 256, 8, lc.sm_count), 256, 0, lc.stream>>>(g.pool.ptr, base, d_touched_bitmap, g.memo.ptr);
-            lc.count();
-            WHARF_CUDA(cudaGetLastError());
-        }
-        else if (!d_touched_bitmap) WHARF_CUDA(cudaMemsetAsync(g.memo.ptr, 0xFF, g.memo.bytes(), lc.stream));
-    }
-    tr.mark("apply: memo invalidation");
     g.pool_used += total;
     g.m = is_delete ? g.m - changed : g.m + changed;
+    if (g.tail)
+    {
+        // fresh rows: filter set, caches empty; every other cache whose cur is a source: emptied
+        aux_build_sources_kernel<<<div_up(ns * 32, 256), 256, 0, lc.stream>>>(b.sources.ptr, ns, g.desc.ptr, g.pool.ptr);
+        aux_invalidate_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr, d_touched_bitmap);
+        lc.count(2);
+        WHARF_CUDA(cudaGetLastError());
+        tr.mark("apply: aux tails");
+    }
 }
 
 void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr, u32* d_col)
 {
     Scratch<u64> deg(lc.stream, g.n + 1);
-    degrees_kernel<<<div_up(g.n + 1, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, deg.ptr);
+    degrees_kernel<<<div_up(g.n + 1, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, 1u, deg.ptr);
     lc.count();
     exclusive_sum(lc, deg.ptr, d_row_ptr, g.n + 1);
     if (d_col) copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, d_row_ptr, d_col);

@@ -28,11 +28,12 @@ struct DevWalkParams
     const RowDesc* __restrict__ desc;
     const u32* __restrict__ pool;
     const u32* __restrict__ version;
-    u32* memo;                        // sampler-state cache aligned with pool (MH node2vec)
+    u32* pool_rw;                     // the pool again, writable: aux tails behind the rows (MH node2vec)
     const u64* __restrict__ draw;
     u32* walks;
     u64 n;
     u64 w_local;
+    u64 first;                        // first local walk of this launch (bulk generation in chunks)
     u32 n_local;
     u32 L;
     u32 rank, world;
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkP
         }
         else
         {
-            w   = t;
+            w   = p.first + t;
             pos = 0;
         }
         const u32 replica = (u32) (w / p.n_local);                  // = walk_id / n  (wharfmh.h:291)
@@ -167,20 +168,30 @@ __global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkP
 
 // ---- Metropolis-Hastings mode ------------------------------------------------------------------------
 //
-// Sampler cache ("memo").  The sampler of state (cur, prev) lives in cur's SamplerManager (graph/vertex.h:12) and,
+// Sampler cache.  The sampler of state (cur, prev) lives in cur's SamplerManager (graph/vertex.h:12) and,
 // because find() hands out copies (wharfmh.h:301,833), never advances past its init value
 // (metropolis_hastings_sampler.h:69-108), a pure function of (seed, cur, prev, version[cur]) and the rows of cur
 // and prev.  A walker in state (cur, prev) has just traversed the edge prev -> cur, whose slot in the row of
-// prev it knows (it picked it), so the cache word of the state lives at memo[begin(prev) + slot]:
-//     bits 0..29  slot of the init value in the row of cur        (vertex = pool[begin(cur) + slot])
-//     bits 30..31 weight class of the init value with respect to prev (node2vec.h:74-88)
-//     0xFFFFFFFF  empty
-// The word dies with the row of prev (fresh rows start empty) and is emptied by invalidate_memo_stream_kernel
-// whenever cur is a batch source (row and version[cur] change, wharfmh.h:504->539).
-constexpr u32 kMemoEmpty = 0xFFFFFFFFu;
-constexpr u32 kNoSlot    = 0xFFFFFFFFu;
-constexpr u32 kSlotMask  = 0x3FFFFFFFu;
+// prev it knows (it picked it), so the cache of the state is the low half of aux word `slot` of the row of prev
+// (aux tails: kernels_graph.cu):
+//     bit  15      valid
+//     bits 13..14  weight class of the init value with respect to prev (node2vec.h:74-88)
+//     bit  12      0: bits 0..11 = slot of the init value in the row of cur (rows up to 4096 neighbours)
+//                  1: bits 0..11 = index of the sampler draw that proposed it (the slot is that draw % degree)
+// The cache dies with the row of prev (fresh tails are zero) and is emptied by aux_invalidate_kernel whenever
+// cur is a batch source (row and version[cur] change, wharfmh.h:504->539).
+constexpr u32 kNoSlot     = 0xFFFFFFFFu;
+constexpr u32 kCacheValid = 0x8000u;
+constexpr u32 kCacheByDraw = 0x1000u;
+constexpr u32 kCacheDirectMax = 4096;     // largest degree whose slots fit bits 0..11
 enum : u32 { kClassReturn = 0, kClassNeighbour = 1, kClassFar = 2 };   // 1/p, 1, 1/q
+
+struct InitValue { u32 cls, slot, draw; };   // weight class, slot in the row of cur, index of the proposing draw
+
+__device__ __forceinline__ u32 cache_encode(InitValue v, u32 degree_cur)
+{
+    return kCacheValid | (v.cls << 13) | (degree_cur <= kCacheDirectMax ? v.slot : (kCacheByDraw | v.draw));
+}
 
 __device__ __forceinline__ float class_weight(const DevWalkParams& p, u32 cls)
 {
@@ -208,6 +219,10 @@ __device__ __forceinline__ u32 row_find(const u32* __restrict__ row, u32 n, u32 
 __device__ __forceinline__ u32 n2v_class(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x)
 {
     if (x == prev) return kClassReturn;
+    if (dprev.degree == 0) return kClassFar;
+    const u32 h = filter_hash(x);
+    const u32 need = filter_bits(h);
+    if (((__ldcg(p.pool_rw + dprev.begin + dprev.degree + filter_block(h, dprev.degree)) >> 16) & need) != need) return kClassFar;   // proven absent
     bool hit;
     row_find(p.pool + dprev.begin, dprev.degree, x, &hit);
     return hit ? kClassNeighbour : kClassFar;
@@ -221,11 +236,12 @@ __device__ __forceinline__ bool mh_accept(float w_old, float w_new, u64 draw)
 }
 
 // MetropolisHastingsSampler::init, strategies RANDOM and BURNIN (metropolis_hastings_sampler.h:72-85), one lane;
-// draws keyed by (seed, cur, prev, version[cur], i).  Returns the cache word.
-__device__ u32 n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
+// draws keyed by (seed, cur, prev, version[cur], i).
+__device__ InitValue n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
 {
     const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
     u64 i = 0;
+    u32 draw = 0;
     const u32* __restrict__ nb = p.pool + dcur.begin;
     u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);                 // RANDOM :72-75
     u32 cls = n2v_class(p, prev, dprev, __ldg(nb + slot));
@@ -233,26 +249,27 @@ __device__ u32 n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dcur, u3
     {
         for (int it = 0; it < 100; it++)
         {
+            const u32 cdraw = (u32) i;
             const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);
             const u32 ccls = n2v_class(p, prev, dprev, __ldg(nb + cslot));
             const float wn = class_weight(p, ccls), wo = class_weight(p, cls);
             bool acc = wo < wn;
             if (!acc) acc = unit_double(keyed_draw(p.seed, kDomSampler, cur, key_b, i++)) <= (double) wn / (double) wo;
-            if (acc) { slot = cslot; cls = ccls; }
+            if (acc) { slot = cslot; cls = ccls; draw = cdraw; }
         }
     }
-    return (cls << 30) | slot;
+    return InitValue{cls, slot, draw};
 }
 
 // MetropolisHastingsSampler::init, strategy WEIGHT (:87-107): the best of 1 + 20 proposals, a strict '>' keeps
 // the first maximum.  Warp-cooperative: the 21 proposals are independent draws (i = 0..20), so lane i evaluates
 // proposal i (one neighbour load + one row search) and a butterfly picks (largest weight, smallest i).
 // All 32 lanes call this with the broadcast state of the walker being served.
-__device__ __forceinline__ u32 n2v_init_weight_warp(const DevWalkParams& p, u32 lane, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
+__device__ __forceinline__ InitValue n2v_init_weight_warp(const DevWalkParams& p, u32 lane, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
 {
     const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
     float w = -1.0f;
-    u32 word = kMemoEmpty;
+    u32 word = 0;                         // (class << 30) | slot
     if (lane < 21)
     {
         const u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, lane), dcur.degree);
@@ -269,7 +286,7 @@ __device__ __forceinline__ u32 n2v_init_weight_warp(const DevWalkParams& p, u32 
         const u32 oidx = __shfl_xor_sync(0xffffffffu, idx, o);
         if (ow > w || (ow == w && oidx < idx)) { w = ow; word = oword; idx = oidx; }
     }
-    return word;
+    return InitValue{word >> 30, word & 0x3FFFFFFFu, idx};
 }
 
 __device__ __forceinline__ u32 warp_max_u32(u32 v)
@@ -286,8 +303,10 @@ __device__ __forceinline__ u32 warp_max_u32(u32 v)
 // search over the ascending row of prev; 32 independent chains per warp keep more loads in flight than a
 // k-ary cooperative search that serialises the warp's queries), and the descriptor of the proposal
 // (speculative: it is the next cur unless the proposal is rejected).  The descriptor of prev is carried.
+// 64 registers -> 4 blocks of 256 per SM.  Capping registers for 5 or 6 resident blocks spills and is slower
+// (measured at scale-20: 35.7 ms at 4 blocks, 37.7 ms at 5, 43.4 ms at 6).
 template <bool kRewalk>
-__global__ void __launch_bounds__(kWalkBlock) walk_n2v_kernel(DevWalkParams p, const u32* __restrict__ affected,
+__global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p, const u32* __restrict__ affected,
                                                               const u32* __restrict__ positions, u64 count,
                                                               unsigned long long* steps_out)
 {
@@ -300,7 +319,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_n2v_kernel(DevWalkParams p, c
     RowDesc d{0, 0}, dprev{0, 0};
     if (owner)
     {
-        if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = t; }
+        if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = p.first + t; }
         const u32 replica = (u32) (w / p.n_local);
         const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
         walk_id = (u64) replica * p.n + start;                       // global id keys the draws
@@ -323,17 +342,19 @@ __global__ void __launch_bounds__(kWalkBlock) walk_n2v_kernel(DevWalkParams p, c
     {
         bool step = owner && !stopped && pos < last_pos;
         if (step && d.degree == 0) { stopped = true; step = false; }              // isolated start (:277-286) or sink
-        u32 cand = 0, cslot = 0, word = kMemoEmpty, cls_new = kClassFar;
+        u32 cand = 0, cslot = 0, cache = 0, cls_new = kClassFar, last_slot = kNoSlot;
         RowDesc dcand{0, 0};
+        u32* aux = p.pool_rw + dprev.begin + dprev.degree;                        // aux tail of the row of prev
         if (step)
         {
-            if (slot != kNoSlot) word = __ldcg(p.memo + dprev.begin + slot);
+            if (slot != kNoSlot) cache = __ldcg(aux + slot) & 0xFFFFu;
             cslot = mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree);   // propose_vertex - node2vec.h:97-105
             cand = __ldg(p.pool + d.begin + cslot);
             dcand = load_desc(p.desc, cand);
             cls_new = n2v_class(p, prev, dprev, cand);
         }
-        const bool need = step && word == kMemoEmpty;
+        const bool need = step && !(cache & kCacheValid);
+        InitValue iv{kClassFar, 0, 0};
         if (p.init_strategy == WMH_INIT_WEIGHT)
         {
             u32 pending = __ballot_sync(0xffffffffu, need);
@@ -344,22 +365,33 @@ __global__ void __launch_bounds__(kWalkBlock) walk_n2v_kernel(DevWalkParams p, c
                 const u32 s_cur = __shfl_sync(0xffffffffu, cur, src), s_prev = __shfl_sync(0xffffffffu, prev, src);
                 const RowDesc s_d{__shfl_sync(0xffffffffu, d.begin, src), __shfl_sync(0xffffffffu, d.degree, src)};
                 const RowDesc s_dp{__shfl_sync(0xffffffffu, dprev.begin, src), __shfl_sync(0xffffffffu, dprev.degree, src)};
-                const u32 r = n2v_init_weight_warp(p, lane, s_cur, s_d, s_prev, s_dp);
-                if ((int) lane == src) word = r;
+                const InitValue r = n2v_init_weight_warp(p, lane, s_cur, s_d, s_prev, s_dp);
+                if ((int) lane == src) iv = r;
             }
         }
-        else if (need) word = n2v_init_serial(p, cur, d, prev, dprev);
-        if (need && slot != kNoSlot) __stcg(p.memo + dprev.begin + slot, word);
+        else if (need) iv = n2v_init_serial(p, cur, d, prev, dprev);
+        if (need)
+        {
+            cache = cache_encode(iv, d.degree);
+            last_slot = iv.slot;
+            if (slot != kNoSlot) __stcg(reinterpret_cast<unsigned short*>(aux + slot), (unsigned short) cache);   // low half only
+        }
         if (step)
         {
             const float wn = class_weight(p, cls_new);                                       // sample :31-46
-            const float wo = class_weight(p, word >> 30);
+            const float wo = class_weight(p, (cache >> 13) & 3u);
             bool acc = wo < wn;
             if (!acc) acc = unit_double(keyed_draw(p.seed, kDomStep, walk_id, pos, 1)) <= (double) wn / (double) wo;
             u32 next = cand;
             if (!acc)
             {
-                cslot = word & kSlotMask;
+                if (last_slot == kNoSlot)
+                {
+                    last_slot = cache & 0xFFFu;
+                    if (cache & kCacheByDraw)                                                 // big row: re-derive the slot from its draw
+                        last_slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, ((u64) prev << 32) | __ldg(p.version + cur), last_slot), d.degree);
+                }
+                cslot = last_slot;
                 next = __ldg(p.pool + d.begin + cslot);
                 dcand = load_desc(p.desc, next);
             }
@@ -392,7 +424,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkPar
     {
         u64 w;
         u32 pos = 0, cur;
-        if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = t; }
+        if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = p.first + t; }
         const u32 replica = (u32) (w / p.n_local);
         const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
         const u64 walk_id = (u64) replica * p.n + start;
@@ -520,12 +552,13 @@ __global__ void fill_u32_kernel(u32* __restrict__ d, u64 count, u32 value)
 DevWalkParams to_dev(const WalkParams& wp)
 {
     DevWalkParams p;
-    p.desc = wp.desc; p.pool = wp.pool; p.version = wp.version; p.memo = wp.memo; p.draw = wp.draw; p.walks = wp.walks;
+    p.desc = wp.desc; p.pool = wp.pool; p.version = wp.version; p.pool_rw = wp.pool_rw; p.draw = wp.draw; p.walks = wp.walks;
     p.n = wp.n; p.w_local = wp.w_local; p.n_local = wp.n_local; p.L = wp.L; p.rank = wp.rank; p.world = wp.world;
     p.init_strategy = wp.init_strategy;
     p.inv_p = 1 / wp.p;                                                 // node2vec.h:78
     p.inv_q = 1 / wp.q;                                                 // node2vec.h:86
     p.seed = wp.seed;
+    p.first = 0;
     return p;
 }
 
@@ -562,12 +595,13 @@ void launch_generate_deterministic(const LaunchCtx& lc, const DevWalkParams& p, 
 }
 
 template <bool kRewalk>
-void launch_walk(const LaunchCtx& lc, const WalkParams& wp, const u32* ids, const u32* positions, u64 count, unsigned long long* d_steps)
+void launch_walk(const LaunchCtx& lc, const WalkParams& wp, const u32* ids, const u32* positions, u64 first, u64 count, unsigned long long* d_steps)
 {
     if (count == 0) return;
-    const DevWalkParams p = to_dev(wp);
+    DevWalkParams p = to_dev(wp);
+    p.first = first;
     const unsigned grid = div_up(count, kWalkBlock);
-    if (wp.deterministic && !kRewalk && det_variant().walks != 0)
+    if (wp.deterministic && !kRewalk && first == 0 && count == wp.w_local && det_variant().walks != 0)
     {
         launch_generate_deterministic(lc, p, d_steps);
         return;
@@ -585,13 +619,18 @@ void launch_walk(const LaunchCtx& lc, const WalkParams& wp, const u32* ids, cons
 
 void walks_generate(const LaunchCtx& lc, const WalkParams& wp, unsigned long long* d_steps)
 {
-    launch_walk<false>(lc, wp, nullptr, nullptr, wp.w_local, d_steps);
+    launch_walk<false>(lc, wp, nullptr, nullptr, 0, wp.w_local, d_steps);
+}
+
+void walks_generate_range(const LaunchCtx& lc, const WalkParams& wp, u64 first, u64 count, unsigned long long* d_steps)
+{
+    launch_walk<false>(lc, wp, nullptr, nullptr, first, count, d_steps);
 }
 
 void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affected, const u32* d_positions, u64 count,
                   unsigned long long* d_steps)
 {
-    launch_walk<true>(lc, wp, d_affected, d_positions, count, d_steps);
+    launch_walk<true>(lc, wp, d_affected, d_positions, 0, count, d_steps);
 }
 
 void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_bitmap, u32* d_min_pos)

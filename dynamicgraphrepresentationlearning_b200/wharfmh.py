@@ -131,6 +131,14 @@ class WharfMH:
         check(self._lib.wmh_generate_initial_random_walks(self._h))
         return self.last_steps()
 
+    def generate_initial_random_walks_to_host(self, out: np.ndarray) -> int:
+        """generate_initial_random_walks with the corpus streamed into `out` ([local_walks, walk_length] uint32, C order;
+        pinned memory overlaps the copies with the walk kernels).  Returns the walker steps."""
+        if out.dtype != np.uint32 or not out.flags["C_CONTIGUOUS"] or out.ndim != 2 or out.shape[1] != self.config.walk_length:
+            raise ValueError("out must be a C-contiguous uint32 array [local_walks, walk_length]")
+        check(self._lib.wmh_generate_initial_random_walks_to_host(self._h, _ptr(out), out.shape[0]))
+        return self.last_steps()
+
     def last_steps(self) -> int:
         return int(self._lib.wmh_last_steps(self._h))
 

@@ -147,6 +147,11 @@ WMH_API int wmh_neighbors(wmh_engine* e, uint32_t vertex, uint32_t* out, uint64_
 
 /* WharfMH::generate_initial_random_walks - graph/wharfmh.h:250. */
 WMH_API int wmh_generate_initial_random_walks(wmh_engine* e);
+/* The same pass with the corpus streamed out while it is generated (what vertex-classification.cpp:167-178 does
+ * after generation, walk by walk): out receives number_of_local_walks rows of walk_length vertices in local walk
+ * order, WMH_NO_VERTEX after a stopped walker.  The device keeps the corpus as after
+ * wmh_generate_initial_random_walks.  Pinned host memory lets the copies overlap the walk kernels. */
+WMH_API int wmh_generate_initial_random_walks_to_host(wmh_engine* e, uint32_t* out, uint64_t capacity_walks);
 /* Walker steps executed by the last generate / batch update (a step = one iteration of wharfmh.h:294). */
 WMH_API uint64_t wmh_last_steps(const wmh_engine* e);
 WMH_API uint64_t wmh_number_of_walks(const wmh_engine* e);               /* global: n * walks_per_vertex */

@@ -207,6 +207,13 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
             detail::check(wmh_generate_initial_random_walks(engine_));
         }
 
+        // Extension: the same pass with the corpus streamed to `out` ([local walks][walk_length]) while it is generated.
+        void generate_initial_random_walks(types::Vertex* out, size_t capacity_walks)
+        {
+            sync_config();
+            detail::check(wmh_generate_initial_random_walks_to_host(engine_, out, capacity_walks));
+        }
+
         std::string walk(types::WalkID walk_id)                                                         // :365
         {
             size_t need = 0;

@@ -478,3 +478,34 @@ def test_coalesced_generation_equals_oracle(wharf, wo, case):
                 full[e.local_walk_ids().astype(np.int64)] = e.walks()
         assert total == steps
         assert np.array_equal(full, o2.walks())
+
+
+@pytest.mark.parametrize("mode", ["det_walker", "det_coalesced", "n2v_mh", "deepwalk_mh", "sharded"])
+def test_generate_to_host_equals_generate_then_copy(wharf, wo, mode):
+    """wmh_generate_initial_random_walks_to_host (generation overlapped with the export) must deliver the corpus that
+    generate + walks() delivers, leave the same corpus on the device, and report the same step count."""
+    import torch
+    n = 1 << 11
+    off, adj = wo.rmat_graph(11, 12000, seed=2)
+    kw = dict(walks_per_vertex=7, walk_length=33)
+    if mode == "det_walker":
+        kw.update(generate_mode=wharf.GENERATE_PER_WALKER)
+    elif mode == "det_coalesced":
+        kw.update(generate_mode=wharf.GENERATE_COALESCED)
+    elif mode == "n2v_mh":
+        kw.update(deterministic_mode=False, random_walk_model=wharf.NODE2VEC, paramP=0.5, paramQ=2.0, seed=5)
+    elif mode == "deepwalk_mh":
+        kw.update(deterministic_mode=False, random_walk_model=wharf.DEEPWALK, seed=5)
+    else:
+        kw.update(rank=1, world=3, generate_mode=wharf.GENERATE_COALESCED)
+    with make(wharf, n, off, adj, **kw) as a, make(wharf, n, off, adj, **kw) as b:
+        steps = a.generate_initial_random_walks()
+        expect = a.walks()
+        out = torch.empty((b.number_of_local_walks(), 33), dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+        out[:] = 7
+        assert b.generate_initial_random_walks_to_host(out) == steps
+        assert np.array_equal(out, expect)
+        assert np.array_equal(b.walks(), expect)
+        pageable = np.zeros_like(expect)
+        assert b.generate_initial_random_walks_to_host(pageable) == steps
+        assert np.array_equal(pageable, expect)

@@ -294,6 +294,12 @@ def main():
     else:
         sample = torch.from_numpy(engine.walks(0, min(20000, engine.number_of_local_walks())).astype(np.int64)).to(dev).t().contiguous()
         bytes_per_step = mh_bytes_per_step(torch, d_offsets, sample) if spec["model"] == "node2vec" else BYTES_PER_DET_STEP
+    if spec["det"]:
+        coalesced = n * 8 + m * 4 > (96 << 20)          # engine's GENERATE_AUTO rule (engine.cu use_coalesced)
+        kernel_name = ("coalesced_{advance,rank,emit}_kernel segments (kernels_coalesced.cu), one generate pass" if coalesced
+                       else "walk_deterministic_ilp_kernel<1,256,0>")
+    else:
+        kernel_name = "walk_n2v_kernel<false>" if spec["model"] == "node2vec" else "walk_deepwalk_mh_kernel<false>"
     steps_per_launch = local_steps / args.steps
     achieved_gbs = steps_per_launch * bytes_per_step / (kernel_avg_ms * 1e-3) / 1e9
     traffic = None
@@ -301,8 +307,14 @@ def main():
     if tpath.exists():
         traffic = json.loads(tpath.read_text()).get(f"{args.workload}:{world}")
     roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": peak_gbs, "unit": "GB/s", "frac": achieved_gbs / peak_gbs,
-                "traffic": traffic, "kernel": "walk_deterministic_kernel<false>" if spec["det"] else f"walk_mh_kernel<{spec['model']},false>",
-                "bytes_per_step": bytes_per_step, "steps_per_launch": steps_per_launch, "kernel_ms": kernel_avg_ms, "peak_source": peak_kind}
+                "traffic": traffic, "kernel": kernel_name,
+                "bytes_per_step": bytes_per_step, "steps_per_launch": steps_per_launch, "kernel_ms": kernel_avg_ms, "peak_source": peak_kind,
+                # the bound the north star names: random 32-B sector gathers from HBM, measured with tools/gather_probe.cu
+                # (profiles/r01c_gather_probe.txt): 37.7 G sectors/s from a 4 GiB table, whatever the policy or occupancy
+                "random_gather": {"peak_gsectors_s": 37.7, "source": "tools/gather_probe.cu, profiles/r01c_gather_probe.txt",
+                                  "dram_fetches_per_s_64B": (traffic["read"] / 64 / (kernel_avg_ms * 1e-3)) if isinstance(traffic, dict) else None}}
+    if isinstance(traffic, dict):
+        roofline["traffic"] = traffic["read"] + traffic["write"]
 
     # ---- deterministic-mode figure beside an MH headline (reference default mode, bit-exact corpus) ----
     extra = {}
@@ -323,7 +335,7 @@ def main():
         det_gbs = (det_steps / args.steps) * BYTES_PER_DET_STEP / (sum(det_ms) / len(det_ms) * 1e-3) / 1e9
         extra["deterministic_mode"] = {"value": det_total / det_s, "unit": "walk-steps/s", "ms_per_step": 1e3 * det_s / args.steps,
                                        "roofline": {"bound": "hbm", "achieved": det_gbs, "peak": peak_gbs, "unit": "GB/s", "frac": det_gbs / peak_gbs,
-                                                    "bytes_per_step": BYTES_PER_DET_STEP, "kernel": "walk_deterministic_kernel<false>"},
+                                                    "bytes_per_step": BYTES_PER_DET_STEP, "kernel": "walk_deterministic_ilp_kernel<1,256,0>"},
                                        "note": "config::deterministic_mode=true (reference default): corpus bit-exact vs the reference"}
         engine.destroy_index()
         engine.set_config(deterministic_mode=False)

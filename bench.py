@@ -197,6 +197,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--updates", type=int, default=4, help="edge batches (insert then delete) to time after the walk benchmark; 0 = skip")
     ap.add_argument("--batch-edges", type=int, default=100000)
+    ap.add_argument("--batch-sweep", default="", help="comma-separated batch sizes (BASELINE config 5): one insert+delete per size instead of --updates batches")
+    ap.add_argument("--insert-only", action="store_true", help="BASELINE config 3: a stream of insert batches, no deletes")
     ap.add_argument("--search", default="auto", choices=["auto", "index", "scan"])
     args = ap.parse_args()
     spec = WORKLOADS[args.workload]
@@ -393,14 +395,15 @@ def main():
         if search == wharf.SEARCH_AUTO:
             pass
         rows = []
-        for b in range(args.updates):
-            d_batch, k = make_batch_on_device(wharf, torch, args.batch_edges, n, b, local_rank)
+        sizes = [int(x) for x in args.batch_sweep.split(",") if x] or [args.batch_edges] * args.updates
+        for b, size in enumerate(sizes):
+            d_batch, k = make_batch_on_device(wharf, torch, size, n, b, local_rank)
             h_batch = torch.empty(2 * k, dtype=torch.int32).pin_memory()
             h_batch.copy_(d_batch)
             torch.cuda.synchronize()
             hb = h_batch.numpy().view(np.uint32).reshape(-1, 2)
             row = {"batch_edges": k}
-            for kind in ("insert", "delete"):
+            for kind in (("insert",) if args.insert_only else ("insert", "delete")):
                 engine.reset_timers()
                 barrier()
                 t0 = time.perf_counter()
@@ -415,7 +418,7 @@ def main():
                              "rewalk_steps": sum_over_ranks(engine.last_steps()), "rewalk_kernel_ms": max_over_ranks(engine.last_walk_kernel_ms())}
             rows.append(row)
         ins = [r["insert"]["latency_ms"] for r in rows]
-        dele = [r["delete"]["latency_ms"] for r in rows]
+        dele = [r["delete"]["latency_ms"] for r in rows if "delete" in r] or [float("nan")]
         updates = {"search": args.search, "batches": rows, "insert_latency_ms_median": statistics.median(ins),
                    "delete_latency_ms_median": statistics.median(dele), "host_batch": True,
                    "note": "latency = host call of wmh_insert/delete_edges_batch (H2D batch, merge, affected search, re-walk), max over ranks"}

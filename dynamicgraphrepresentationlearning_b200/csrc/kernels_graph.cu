@@ -535,6 +535,9 @@ void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g)
     if (g.tail) return;
     g.tail = 1;
     graph_compact(lc, g, 0);
+    // the pool the rows just left is too small to be the next compaction's target: size the spare now, while the
+    // caller is still setting up a corpus, instead of inside an edge batch
+    if (g.spare.count < g.pool.count) g.spare.allocate(g.pool.count);
 }
 
 void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch& b, bool is_delete, u32* d_touched_bitmap)

@@ -262,24 +262,49 @@ __device__ InitValue n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dc
 }
 
 // MetropolisHastingsSampler::init, strategy WEIGHT (:87-107): the best of 1 + 20 proposals, a strict '>' keeps
-// the first maximum.  Warp-cooperative: the 21 proposals are independent draws (i = 0..20), so lane i evaluates
-// proposal i (one neighbour load + one row search) and a butterfly picks (largest weight, smallest i).
-// All 32 lanes call this with the broadcast state of the walker being served.
-__device__ __forceinline__ InitValue n2v_init_weight_warp(const DevWalkParams& p, u32 lane, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
+// the first maximum.  Warp-cooperative: the 21 proposals are independent keyed draws (i = 0..20), so a group of 8
+// lanes serves one walker - lane `sub` evaluates proposals sub, sub + 8, sub + 16 (three independent load chains:
+// neighbour, then filter block) and a butterfly over the group picks (largest weight, smallest i).  The four
+// groups of a warp serve four walkers at once.  Every lane calls this with the state of its group's walker.
+__device__ __forceinline__ InitValue n2v_init_weight_group(const DevWalkParams& p, u32 sub, bool has, u32 cur, RowDesc dcur, u32 prev, RowDesc dprev)
 {
-    const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
     float w = -1.0f;
-    u32 word = 0;                         // (class << 30) | slot
-    if (lane < 21)
+    u32 word = 0, idx = 0xFFFFFFFFu;      // word = (class << 30) | slot
+    if (has)
     {
-        const u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, lane), dcur.degree);
-        const u32 cls = n2v_class(p, prev, dprev, __ldg(p.pool + dcur.begin + slot));
-        w = class_weight(p, cls);
-        word = (cls << 30) | slot;
-    }
-    u32 idx = lane;
+        const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
+        const u32* aux = p.pool_rw + dprev.begin + dprev.degree;
+        u32 slot[3], x[3], fh[3], fw[3];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
+        for (u32 k = 0; k < 3; k++) slot[k] = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, sub + 8 * k), dcur.degree);
+#pragma unroll
+        for (u32 k = 0; k < 3; k++) x[k] = __ldg(p.pool + dcur.begin + slot[k]);
+#pragma unroll
+        for (u32 k = 0; k < 3; k++)
+        {
+            fh[k] = filter_hash(x[k]);
+            fw[k] = dprev.degree ? __ldcg(aux + filter_block(fh[k], dprev.degree)) >> 16 : 0u;
+        }
+#pragma unroll
+        for (u32 k = 0; k < 3; k++)
+        {
+            const u32 i = sub + 8 * k;
+            if (i >= 21) break;
+            u32 cls = kClassFar;
+            const u32 need = filter_bits(fh[k]);
+            if (x[k] == prev) cls = kClassReturn;
+            else if (dprev.degree && (fw[k] & need) == need)
+            {
+                bool hit;
+                row_find(p.pool + dprev.begin, dprev.degree, x[k], &hit);
+                if (hit) cls = kClassNeighbour;
+            }
+            const float wk = class_weight(p, cls);
+            if (wk > w) { w = wk; word = (cls << 30) | slot[k]; idx = i; }
+        }
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1)
     {
         const float ow = __shfl_xor_sync(0xffffffffu, w, o);
         const u32 oword = __shfl_xor_sync(0xffffffffu, word, o);
@@ -358,15 +383,23 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
         if (p.init_strategy == WMH_INIT_WEIGHT)
         {
             u32 pending = __ballot_sync(0xffffffffu, need);
-            while (pending)
+            while (pending)                                   // four walkers per round, one per 8-lane group
             {
-                const int src = __ffs(pending) - 1;
-                pending &= pending - 1;
+                u32 mine = pending;                           // pending with the first (lane / 8) bits dropped
+                for (u32 g = lane >> 3; g && mine; --g) mine &= mine - 1;
+                const bool has = mine != 0;
+                const int src = has ? __ffs(mine) - 1 : 0;
                 const u32 s_cur = __shfl_sync(0xffffffffu, cur, src), s_prev = __shfl_sync(0xffffffffu, prev, src);
                 const RowDesc s_d{__shfl_sync(0xffffffffu, d.begin, src), __shfl_sync(0xffffffffu, d.degree, src)};
                 const RowDesc s_dp{__shfl_sync(0xffffffffu, dprev.begin, src), __shfl_sync(0xffffffffu, dprev.degree, src)};
-                const InitValue r = n2v_init_weight_warp(p, lane, s_cur, s_d, s_prev, s_dp);
-                if ((int) lane == src) iv = r;
+                const InitValue r = n2v_init_weight_group(p, lane & 7, has, s_cur, s_d, s_prev, s_dp);
+                // a served walker is the k-th pending lane (k < 4): its result sits in every lane of group k
+                const u32 my_rank = __popc(pending & ((1u << lane) - 1u));
+                const int from = (int) ((my_rank & 3u) * 8u);
+                const InitValue got{__shfl_sync(0xffffffffu, r.cls, from), __shfl_sync(0xffffffffu, r.slot, from), __shfl_sync(0xffffffffu, r.draw, from)};
+                if (((pending >> lane) & 1u) && my_rank < 4) iv = got;
+#pragma unroll
+                for (int k = 0; k < 4; k++) pending &= pending - 1;
             }
         }
         else if (need) iv = n2v_init_serial(p, cur, d, prev, dprev);

@@ -106,6 +106,7 @@ namespace config   // config/globals.h:7-29
     // additions of this engine
     inline int device                 = 0;
     inline int search_mode            = WMH_SEARCH_AUTO;
+    inline int generate_mode          = WMH_GENERATE_AUTO;      // schedule of deterministic bulk generation (same corpus)
 }
 
 namespace dynamic_graph_representation_learning_with_metropolis_hastings
@@ -127,6 +128,7 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
             c.init_strategy = config::sampler_init_strategy == types::RANDOM ? WMH_INIT_RANDOM
                             : config::sampler_init_strategy == types::BURNIN ? WMH_INIT_BURNIN : WMH_INIT_WEIGHT;
             c.search_mode = static_cast<uint32_t>(config::search_mode);
+            c.generate_mode = static_cast<uint32_t>(config::generate_mode);
             c.seed = config::random_seed;
             c.device = config::device;
             return c;

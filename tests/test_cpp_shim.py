@@ -1,0 +1,43 @@
+"""The C++ re-creation of dygrl::WharfMH (include/wharfmh_b200.hpp) must compile as ordinary C++17 against the C ABI
+and, on a B200, reproduce the reference's corpora when it is driven like the reference's own tests
+(tests/sampler.cpp fixture; goldens from the unmodified reference in tests/golden/golden.json)."""
+import json
+import subprocess
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+LIB_DIR = ROOT / "dynamicgraphrepresentationlearning_b200" / "lib"
+BUILD = ROOT / "tests" / "cpp" / "_build"
+
+
+def build_driver() -> Path:
+    BUILD.mkdir(parents=True, exist_ok=True)
+    exe = BUILD / "shim_driver"
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", f"-I{ROOT / 'include'}", str(ROOT / "tests" / "cpp" / "shim_driver.cpp"),
+                    "-o", str(exe), f"-L{LIB_DIR}", "-lwharfmh_b200", f"-Wl,-rpath,{LIB_DIR}"], check=True)
+    return exe
+
+
+def test_cpp_shim_compiles_and_fails_loudly_without_gpu():
+    exe = build_driver()
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by test_cpp_shim_reproduces_reference_corpora")
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU path" in r.stderr          # no silent fallback
+
+
+@pytest.mark.gpu
+def test_cpp_shim_reproduces_reference_corpora():
+    exe = build_driver()
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines()
+    six = json.loads((ROOT / "tests" / "golden" / "golden.json").read_text())["six"]
+    for tag, walks in zip(("initial", "inserted", "deleted"), six["walks"]):
+        got = [l.split(": ", 1)[1] for l in out if l.startswith(tag + " ")]
+        assert got == ["".join(f"{v} " for v in w) for w in walks], tag     # WharfMH::walk format, wharfmh.h:376
+    assert "vertex_at_walk(2,3) = 3" in out
+    assert "insert affected 12 first (0,3) edges 20" in out                  # caller's batch sorted in place (:452)
+    assert "delete affected 12 edges 18" in out
+    assert "degree(2) = 5" in out

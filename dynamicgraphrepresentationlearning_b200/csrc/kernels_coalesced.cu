@@ -4,18 +4,23 @@
 // In deterministic mode every walk of replica r = walk_id / n consumes the same draw X[r][pos] at position pos,
 // so the step is a function of the vertex alone:  F_{r,pos}(u) = N(u)[ X[r][pos] % deg(u) ].  Two walkers of a
 // replica that ever stand on the same vertex at the same position are identical from there on.  On RMAT graphs
-// the n walkers of a replica collapse quickly (43 % distinct vertices after one step, 4 % after ten, 2.5 % on
+// the n walkers of a replica collapse quickly (46 % distinct vertices after one step, 5 % after ten, 3 % on
 // average over 80 positions; measured), so instead of two dependent random DRAM loads per
 // walker step this path keeps, per replica, the CLASSES (groups of walkers on the same vertex) and works in
-// SEGMENTS of k <= 8 consecutive positions:
-//   advance  one thread per class walks its vertex k steps and writes the k vertices class-major:
-//            trail[c][0..k) (one 32-byte sector per class) and marks the final vertex in a bitmap;
-//   rank     a prefix sum over the bitmap's word popcounts numbers the occupied vertices in ascending order:
-//            that number is the class of the next segment (classes that met share it), so the next advance reads
-//            descriptors and rows in ascending address order;
-//   emit     one thread per walker loads the sector of its class once and stores k corpus cells
-//            walks[pos + 1 + j][i] = trail[cls[i]][j]  (coalesced per row), then moves to its merged class.
-// Segment lengths grow 1,1,1,1,2,2,4,4,8,8,... because the class count falls fastest at the first positions.
+// SEGMENTS of k <= 7 consecutive positions.  A class owns one RECORD of R = 2, 4 or 8 words: the R - 1 vertices of
+// the segment followed by the class it belongs to in the next segment, so a walker needs ONE aligned vector load
+// (8, 16 or 32 bytes: never more than one sector) per segment:
+//   advance  one thread per class walks its vertex k steps, writes them into the record and marks the final
+//            vertex in a bitmap;
+//   scan     exclusive prefix sum over the bitmap's word popcounts: the rank of an occupied vertex among the
+//            occupied vertices is the class of the next segment (classes that met share it, and class order =
+//            vertex order, so the next advance reads descriptors and rows at ascending addresses);
+//   expand   one thread per bitmap word writes the vertices of the next classes (ascending), the (rank, bits)
+//            table used by relabel, and clears the word;
+//   relabel  one thread per class writes the next class into the last word of its record;
+//   emit     one thread per walker loads the record of its class and stores the segment's corpus cells
+//            walks[pos + 1 + j][i] = record[cls[i]][j]  (coalesced per row), then moves to the next class.
+// Segment lengths grow 1,1,1,1,3,3,3,7,7,... because the class count falls fastest at the first positions.
 // The corpus is bit-identical to the one-walker-per-thread kernel (tests/test_gpu_parity.py).
 #include "engine.hpp"
 
@@ -30,14 +35,43 @@ namespace wharf
 namespace
 {
 constexpr int kBlock = 256;
-constexpr u32 kMaxSeg = 8;          // positions per segment: 8 x 4 B = one sector per class
+constexpr u32 kMaxRec = 8;          // words per class record: 7 vertices + next class = one 32-byte sector
 
-struct SegDraws { u64 x[kMaxSeg]; };
+struct SegDraws { u64 x[kMaxRec]; };
 
 __device__ __forceinline__ RowDesc ld_desc(const RowDesc* __restrict__ desc, u32 v)
 {
     const uint2 t = __ldg(reinterpret_cast<const uint2*>(desc) + v);
     return RowDesc{t.x, t.y};
+}
+
+template <u32 R> struct Record;
+template <> struct Record<2> { using vec = uint2; };
+template <> struct Record<4> { using vec = uint4; };
+template <> struct Record<8> { using vec = uint4; };
+
+template <u32 R>
+__device__ __forceinline__ void load_record(const u32* __restrict__ rec, u32 c, u32 (&t)[R])
+{
+    if constexpr (R == 2) { const uint2 a = __ldg(reinterpret_cast<const uint2*>(rec) + c); t[0] = a.x; t[1] = a.y; }
+    else if constexpr (R == 4) { const uint4 a = __ldg(reinterpret_cast<const uint4*>(rec) + c); t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; }
+    else
+    {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(rec) + 2 * (u64) c), b = __ldg(reinterpret_cast<const uint4*>(rec) + 2 * (u64) c + 1);
+        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
+    }
+}
+
+template <u32 R>
+__device__ __forceinline__ void store_record(u32* __restrict__ rec, u32 c, const u32 (&t)[R])
+{
+    if constexpr (R == 2) reinterpret_cast<uint2*>(rec)[c] = make_uint2(t[0], t[1]);
+    else if constexpr (R == 4) reinterpret_cast<uint4*>(rec)[c] = make_uint4(t[0], t[1], t[2], t[3]);
+    else
+    {
+        reinterpret_cast<uint4*>(rec)[2 * (u64) c] = make_uint4(t[0], t[1], t[2], t[3]);
+        reinterpret_cast<uint4*>(rec)[2 * (u64) c + 1] = make_uint4(t[4], t[5], t[6], t[7]);
+    }
 }
 
 // cls[i] = i, vertex of class i = start vertex of local walker i, first corpus row of the replica.
@@ -53,34 +87,31 @@ __global__ void __launch_bounds__(kBlock) coalesced_init_kernel(u32* __restrict_
     row0[i] = v;
 }
 
-// trail[c][j] = vertex of class c after j + 1 steps from cv[c]; a class on a degree-0 vertex (isolated start or
-// sink) turns into kNoVertex and stays there.  The final vertex is marked for the merge.
-template <u32 K>
+// record[c][j] = vertex of class c after j + 1 steps from cv[c], j < k; a class on a degree-0 vertex (isolated
+// start or sink) turns into kNoVertex and stays there.  The final vertex is marked for the merge.
+template <u32 R>
 __global__ void __launch_bounds__(kBlock) coalesced_advance_kernel(const RowDesc* __restrict__ desc, const u32* __restrict__ pool, const u32* __restrict__ cv,
-                                                                   const u32* __restrict__ n_classes, SegDraws draws, u32* __restrict__ trail,
+                                                                   const u32* __restrict__ n_classes, SegDraws draws, u32 k, u32* __restrict__ rec,
                                                                    u32* __restrict__ bitmap)
 {
     const u32 nc = *n_classes;
     for (u32 c = blockIdx.x * kBlock + threadIdx.x; c < nc; c += gridDim.x * kBlock)
     {
         u32 u = cv[c];
-        u32 t[K];
+        u32 t[R];
 #pragma unroll
-        for (u32 j = 0; j < K; j++)
+        for (u32 j = 0; j < R - 1; j++)
         {
-            if (u != kNoVertex)
+            if (j < k && u != kNoVertex)
             {
                 const RowDesc d = ld_desc(desc, u);
                 u = d.degree ? __ldg(pool + d.begin + mod_u64_u32(draws.x[j], d.degree)) : kNoVertex;
             }
-            t[j] = u;
+            t[j] = j < k ? u : kNoVertex;
         }
-        u32* out = trail + (u64) c * K;
-        if constexpr (K == 8) { reinterpret_cast<uint4*>(out)[0] = make_uint4(t[0], t[1], t[2], t[3]); reinterpret_cast<uint4*>(out)[1] = make_uint4(t[4], t[5], t[6], t[7]); }
-        else if constexpr (K == 4) reinterpret_cast<uint4*>(out)[0] = make_uint4(t[0], t[1], t[2], t[3]);
-        else if constexpr (K == 2) reinterpret_cast<uint2*>(out)[0] = make_uint2(t[0], t[1]);
-        else out[0] = t[0];
-        if (u != kNoVertex) atomicOr(bitmap + (u >> 5), 1u << (u & 31));
+        t[R - 1] = u;                                  // final vertex; relabel turns it into the next class
+        store_record<R>(rec, c, t);
+        if (bitmap && u != kNoVertex) atomicOr(bitmap + (u >> 5), 1u << (u & 31));
     }
 }
 
@@ -91,57 +122,70 @@ struct PopcountOf
     __device__ u32 operator()(u32 w) const { return w < words ? (u32) __popc(bitmap[w]) : 0u; }
 };
 
-// New class of every class = rank of its final vertex among the marked vertices; dead classes share the extra
-// class `total`.  Also lays down the vertices of the next classes (ascending) and their count.
-template <u32 K>
-__global__ void __launch_bounds__(kBlock) coalesced_rank_kernel(const u32* __restrict__ trail, const u32* __restrict__ bitmap, const u32* __restrict__ word_rank,
-                                                                u32 words, u32* __restrict__ new_class, u32* __restrict__ cv_next,
-                                                                const u32* __restrict__ n_classes, u32* __restrict__ n_classes_next)
+// One thread per bitmap word: the occupied vertices, in ascending order, are the classes of the next segment.
+// Leaves table[w] = (rank of the word's first occupied vertex, the word's bits) for relabel and clears the bitmap.
+__global__ void __launch_bounds__(kBlock) coalesced_expand_kernel(u32* __restrict__ bitmap, const u32* __restrict__ word_rank, u32 words,
+                                                                  uint2* __restrict__ table, u32* __restrict__ cv_next, u32* __restrict__ n_classes_next)
+{
+    const u32 w = blockIdx.x * kBlock + threadIdx.x;
+    if (w == 0)
+    {
+        const u32 total = word_rank[words];
+        cv_next[total] = kNoVertex;                    // the class of every walker that stopped
+        *n_classes_next = total + 1;
+    }
+    if (w >= words) return;
+    u32 bits = bitmap[w];
+    const u32 r = word_rank[w];
+    table[w] = make_uint2(r, bits);
+    if (!bits) return;
+    bitmap[w] = 0;
+    u32* out = cv_next + r;
+    while (bits)
+    {
+        *out++ = (w << 5) + (u32) (__ffs(bits) - 1);
+        bits &= bits - 1;
+    }
+}
+
+// Last word of every record: final vertex -> its rank among the occupied vertices (dead classes share `total`).
+template <u32 R>
+__global__ void __launch_bounds__(kBlock) coalesced_relabel_kernel(u32* __restrict__ rec, const uint2* __restrict__ table, const u32* __restrict__ word_rank,
+                                                                   u32 words, const u32* __restrict__ n_classes)
 {
     const u32 nc = *n_classes;
     const u32 total = word_rank[words];
     for (u32 c = blockIdx.x * kBlock + threadIdx.x; c < nc; c += gridDim.x * kBlock)
     {
-        const u32 v = trail[(u64) c * K + (K - 1)];
+        u32* slot = rec + (u64) c * R + (R - 1);
+        const u32 v = *slot;
         u32 r = total;
-        if (v != kNoVertex) r = word_rank[v >> 5] + (u32) __popc(bitmap[v >> 5] & ((1u << (v & 31)) - 1u));
-        new_class[c] = r;
-        cv_next[r] = v;                                // classes that met write the same value
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0)
-    {
-        cv_next[total] = kNoVertex;
-        *n_classes_next = total + 1;
+        if (v != kNoVertex)
+        {
+            const uint2 e = __ldg(table + (v >> 5));
+            r = e.x + (u32) __popc(e.y & ((1u << (v & 31)) - 1u));
+        }
+        *slot = r;
     }
 }
 
-// Corpus cells of the segment: walks[first_row + j][i] = trail[cls[i]][j] for j < stored (the draw at the last
-// position is unobservable, wharfmh.h:315-317: it is counted, not stored), then the walker moves to its merged
-// class.  Every trail entry that holds a vertex is one step.
-template <u32 K, bool kRelabel>
-__global__ void __launch_bounds__(kBlock) coalesced_emit_kernel(u32* __restrict__ cls, const u32* __restrict__ trail, const u32* __restrict__ new_class,
-                                                                u32* __restrict__ first_row, u64 row_stride, u32 stored, u32 n_local,
-                                                                unsigned long long* __restrict__ steps_out)
+// Corpus cells of the segment: walks[first_row + j][i] = record[cls[i]][j] for j < stored (the draw at the last
+// position is unobservable, wharfmh.h:315-317: it is counted, not stored), then the walker moves to its next
+// class.  Every record entry that holds a vertex is one step.
+template <u32 R, bool kRelabel>
+__global__ void __launch_bounds__(kBlock) coalesced_emit_kernel(u32* __restrict__ cls, const u32* __restrict__ rec, u32* __restrict__ first_row,
+                                                                u64 row_stride, u32 stored, u32 n_local, unsigned long long* __restrict__ steps_out)
 {
     const u32 i = blockIdx.x * kBlock + threadIdx.x;
     u32 moved = 0;
     if (i < n_local)
     {
-        const u32 c = cls[i];
-        u32 t[K];
-        const u32* src = trail + (u64) c * K;
-        if constexpr (K == 8)
-        {
-            const uint4 a = __ldg(reinterpret_cast<const uint4*>(src)), b = __ldg(reinterpret_cast<const uint4*>(src) + 1);
-            t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
-        }
-        else if constexpr (K == 4) { const uint4 a = __ldg(reinterpret_cast<const uint4*>(src)); t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; }
-        else if constexpr (K == 2) { const uint2 a = __ldg(reinterpret_cast<const uint2*>(src)); t[0] = a.x; t[1] = a.y; }
-        else t[0] = __ldg(src);
-        if (kRelabel) cls[i] = __ldg(new_class + c);
+        u32 t[R];
+        load_record<R>(rec, __ldcs(cls + i), t);
+        if (kRelabel) __stcs(cls + i, t[R - 1]);
         u32* out = first_row + i;
 #pragma unroll
-        for (u32 j = 0; j < K; j++)
+        for (u32 j = 0; j < R - 1; j++)
         {
             if (j < stored) __stcs(out + (u64) j * row_stride, t[j]);
             moved += t[j] != kNoVertex;
@@ -150,32 +194,28 @@ __global__ void __launch_bounds__(kBlock) coalesced_emit_kernel(u32* __restrict_
     block_add_u64(steps_out, moved);
 }
 
-// Segment length at advance index a (the advance that produces the vertex of position a + 1).
-u32 segment_length(u32 a, u32 remaining)
-{
-    const u32 want = a < 4 ? 1 : (a < 8 ? 2 : (a < 16 ? 4 : kMaxSeg));
-    u32 k = 1;
-    while (k * 2 <= want && k * 2 <= remaining) k *= 2;
-    return k;
-}
+// Record size (words) of the segment whose first advance index is a: R - 1 positions per segment.
+u32 record_words(u32 a) { return a < 4 ? 2 : (a < 13 ? 4 : kMaxRec); }
 
 struct SegmentCtx
 {
     const LaunchCtx& lc;
     const WalkParams& wp;
     u32 words;
-    unsigned walker_grid, class_grid;
-    u32 *cls, *trail, *new_class, *bitmap, *word_rank;
+    unsigned walker_grid, class_grid, word_grid;
+    u32 *cls, *rec, *bitmap, *word_rank;
+    uint2* table;
     void* scan_temp;
     size_t scan_temp_bytes;
     unsigned long long* d_steps;
 };
 
-template <u32 K>
-void run_segment(const SegmentCtx& s, const SegDraws& draws, const u32* cv, u32* cv_next, const u32* nc, u32* nc_next, u32* first_row, u32 stored, bool merge)
+template <u32 R>
+void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* cv, u32* cv_next, const u32* nc, u32* nc_next, u32* first_row, u32 stored,
+                 bool merge)
 {
     const LaunchCtx& lc = s.lc;
-    coalesced_advance_kernel<K><<<s.class_grid, kBlock, 0, lc.stream>>>(s.wp.desc, s.wp.pool, cv, nc, draws, s.trail, s.bitmap);
+    coalesced_advance_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.wp.desc, s.wp.pool, cv, nc, draws, k, s.rec, merge ? s.bitmap : nullptr);
     lc.count();
     if (merge)
     {
@@ -184,14 +224,14 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, const u32* cv, u32*
         size_t bytes = s.scan_temp_bytes;
         WHARF_CUDA(cub::DeviceScan::ExclusiveSum(s.scan_temp, bytes, pops, s.word_rank, (int) (s.words + 1), lc.stream));
         lc.count_lib();
-        coalesced_rank_kernel<K><<<s.class_grid, kBlock, 0, lc.stream>>>(s.trail, s.bitmap, s.word_rank, s.words, s.new_class, cv_next, nc, nc_next);
-        coalesced_emit_kernel<K, true><<<s.walker_grid, kBlock, 0, lc.stream>>>(s.cls, s.trail, s.new_class, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
-        lc.count(2);
-        WHARF_CUDA(cudaMemsetAsync(s.bitmap, 0, (u64) s.words * 4, lc.stream));
+        coalesced_expand_kernel<<<s.word_grid, kBlock, 0, lc.stream>>>(s.bitmap, s.word_rank, s.words, s.table, cv_next, nc_next);
+        coalesced_relabel_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.rec, s.table, s.word_rank, s.words, nc);
+        coalesced_emit_kernel<R, true><<<s.walker_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
+        lc.count(3);
     }
     else
     {
-        coalesced_emit_kernel<K, false><<<s.walker_grid, kBlock, 0, lc.stream>>>(s.cls, s.trail, nullptr, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
+        coalesced_emit_kernel<R, false><<<s.walker_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
         lc.count();
     }
 }
@@ -203,9 +243,10 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
     if (wp.w_local == 0) return;
     const u32 nl = wp.n_local, L = wp.L;
     const u32 words = (u32) ((wp.n + 31) / 32);
-    Scratch<u32> cls(lc.stream, nl), cv_a(lc.stream, (u64) nl + 1), cv_b(lc.stream, (u64) nl + 1), new_class(lc.stream, (u64) nl + 1);
-    Scratch<u32> trail(lc.stream, ((u64) nl + 1) * kMaxSeg);
+    Scratch<u32> cls(lc.stream, nl), cv_a(lc.stream, (u64) nl + 1), cv_b(lc.stream, (u64) nl + 1);
+    Scratch<u32> rec(lc.stream, ((u64) nl + 1) * kMaxRec);
     Scratch<u32> bitmap(lc.stream, words), word_rank(lc.stream, (u64) words + 1), counts(lc.stream, 2);
+    Scratch<uint2> table(lc.stream, words);
     WHARF_CUDA(cudaMemsetAsync(bitmap.ptr, 0, (u64) words * 4, lc.stream));
 
     size_t temp_bytes = 0;
@@ -216,8 +257,8 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
     }
     Scratch<u8> temp(lc.stream, temp_bytes);
 
-    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), grid_for(nl, kBlock, 8, lc.sm_count), cls.ptr, trail.ptr, new_class.ptr, bitmap.ptr,
-                 word_rank.ptr, temp.ptr, temp_bytes, d_steps};
+    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock), cls.ptr, rec.ptr, bitmap.ptr,
+                 word_rank.ptr, table.ptr, temp.ptr, temp_bytes, d_steps};
     for (u32 r = 0; r < wp.wpv; r++)
     {
         u32 *cv = cv_a.ptr, *cv_next = cv_b.ptr, *nc = counts.ptr, *nc_next = counts.ptr + 1;
@@ -226,18 +267,18 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
         lc.count();
         for (u32 a = 0; a < L;)
         {
-            const u32 k = segment_length(a, L - a);
+            const u32 R = record_words(a);
+            const u32 k = std::min(R - 1, L - a);                 // draws a .. a + k - 1
             SegDraws draws{};
             for (u32 j = 0; j < k; j++) draws.x[j] = host_draw[(u64) r * L + a + j];
             const u32 stored = std::min(k, L - 1 - a);            // cells a + 1 .. a + stored exist; the last draw is only counted
             const bool merge = a + k < L;
             u32* first_row = col + (u64) (a + 1) * wp.w_local;
-            switch (k)
+            switch (R)
             {
-                case 1: run_segment<1>(s, draws, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
-                case 2: run_segment<2>(s, draws, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
-                case 4: run_segment<4>(s, draws, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
-                default: run_segment<8>(s, draws, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+                case 2: run_segment<2>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+                case 4: run_segment<4>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+                default: run_segment<8>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
             }
             if (merge) { std::swap(cv, cv_next); std::swap(nc, nc_next); }
             a += k;

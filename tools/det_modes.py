@@ -1,5 +1,5 @@
 """Times deterministic bulk generation in both schedules (GENERATE_PER_WALKER / GENERATE_COALESCED) on a bench workload
-and checks that the corpus fingerprints agree.     python tools/det_modes.py [workload=dw25] [iters=3]"""
+and checks that the corpus fingerprints agree.     python tools/det_modes.py [workload=dw25] [iters=3] [only=coalesced|per_walker]"""
 import json
 import sys
 from pathlib import Path
@@ -13,11 +13,14 @@ import dynamicgraphrepresentationlearning_b200 as wharf  # noqa: E402
 
 workload = sys.argv[1] if len(sys.argv) > 1 else "dw25"
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+only = sys.argv[3] if len(sys.argv) > 3 else ""          # "coalesced" / "per_walker": time one schedule only (ncu launch lists)
 spec = bench.WORKLOADS[workload]
 n, m, off, adj = bench.make_graph_on_device(wharf, torch, spec, 0)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 fps = {}
 for name, mode in (("per_walker", wharf.GENERATE_PER_WALKER), ("coalesced", wharf.GENERATE_COALESCED)):
+    if only and name != only:
+        continue
     cfg = wharf.Config(walks_per_vertex=10, walk_length=80, random_walk_model=wharf.DEEPWALK, deterministic_mode=True,
                        search_mode=wharf.SEARCH_SCAN, generate_mode=mode)
     e = wharf.WharfMH(n, m, off.data_ptr(), adj.data_ptr(), config=cfg, device_arrays=True)
@@ -34,4 +37,4 @@ for name, mode in (("per_walker", wharf.GENERATE_PER_WALKER), ("coalesced", whar
                       "gsteps_s": round(steps / avg / 1e6, 2), "frac_of_68B_roofline": round(steps * 68 / (avg * 1e-3) / 1e9 / 6553.3, 4),
                       "launches": e.kernel_launches(), "fingerprint": fps[name]}), flush=True)
     e.destroy()
-assert fps["per_walker"] == fps["coalesced"], "schedules disagree"
+assert only or fps["per_walker"] == fps["coalesced"], "schedules disagree"

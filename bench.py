@@ -200,6 +200,7 @@ def main():
     ap.add_argument("--batch-sweep", default="", help="comma-separated batch sizes (BASELINE config 5): one insert+delete per size instead of --updates batches")
     ap.add_argument("--insert-only", action="store_true", help="BASELINE config 3: a stream of insert batches, no deletes")
     ap.add_argument("--search", default="auto", choices=["auto", "index", "scan"])
+    ap.add_argument("--no-peers", action="store_true", help="N > 1: do not map peer memory (every rank computes all sampler init values itself)")
     args = ap.parse_args()
     spec = WORKLOADS[args.workload]
     if args.warmup < 3:
@@ -258,6 +259,10 @@ def main():
     cfg = wharf.Config(walks_per_vertex=WPV, walk_length=LEN, random_walk_model=model, paramP=P, paramQ=Q,
                        deterministic_mode=spec["det"], seed=1, search_mode=wharf.SEARCH_SCAN, device=local_rank, rank=rank, world=world)
     engine = wharf.WharfMH(n, m, d_offsets.data_ptr(), d_edges.data_ptr(), config=cfg, device_arrays=True)
+    peers = False
+    if 1 < world <= 8 and not args.no_peers:
+        from dynamicgraphrepresentationlearning_b200.distributed import connect_peers
+        peers = connect_peers(engine)                                    # exchange buffers mapped between the ranks (NVLink)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
 
     def one_step():
@@ -280,6 +285,7 @@ def main():
         barrier()
         wall = time.perf_counter() - wall0
     launches = engine.kernel_launches() - launches0
+    peer_exchanges = engine.peer_exchanges()
     device_s = max_over_ranks(sum(kernel_ms) * 1e-3)
     total_steps = sum_over_ranks(local_steps)
     value = total_steps / device_s
@@ -439,7 +445,9 @@ def main():
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": spec["desc"], "generator": "utility::generate_batch_of_edges(E/2, V, seed 42, a=.5,b=.2,c=.1, symmetric) restated on device",
                        "n": n, "m": m, "walks_per_vertex": WPV, "walk_length": LEN, "deterministic_mode": spec["det"],
-                       "parallelism": f"walks sharded by start vertex over {world} rank(s), graph replicated",
+                       "parallelism": f"walks sharded by start vertex over {world} rank(s), graph replicated"
+                                      + (", sampler init values computed once per box and stored into the peers over NVLink" if peers else ""),
+                       "peer_exchanges": peer_exchanges,
                        "l2": "explicit 256 MiB write between timed steps"},
             "clocks": clocks.summary(), "gpu_launches": launches, "wall_s_timed_region": wall,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "updates": updates,

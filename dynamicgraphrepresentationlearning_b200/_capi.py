@@ -20,6 +20,7 @@ DEEPWALK, NODE2VEC = 0, 1
 INIT_RANDOM, INIT_BURNIN, INIT_WEIGHT = 0, 1, 2
 SEARCH_AUTO, SEARCH_INDEX, SEARCH_SCAN = 0, 1, 2
 GENERATE_AUTO, GENERATE_PER_WALKER, GENERATE_COALESCED = 0, 1, 2
+PEER_HANDLE_BYTES, PEER_MAX_WORLD = 64, 8
 TIMER_GRAPH_UPDATE_INSERT, TIMER_WALK_UPDATE_INSERT, TIMER_GRAPH_UPDATE_DELETE, TIMER_WALK_UPDATE_DELETE, TIMER_GENERATE = range(5)
 
 
@@ -113,6 +114,11 @@ SIGNATURES = {
     "wmh_stream": (vp, [vp]),
     "wmh_synchronize": (i32, [vp]),
     "wmh_trim_memory": (i32, [i32]),
+    "wmh_peer_create": (i32, [vp, u64, vp]),
+    "wmh_peer_attach": (i32, [vp, vp]),
+    "wmh_peer_detach": (i32, [vp]),
+    "wmh_peer_bytes_needed": (u64, [vp]),
+    "wmh_peer_exchanges": (u64, [vp]),
     "wmh_generate_batch_of_edges_device": (i32, [i32, u64, u64, u64, i32, i32, C.c_double, C.c_double, C.c_double, vp, PU64]),
     "wmh_pairs_to_csr_device": (i32, [i32, u64, vp, u64, vp, vp]),
 }

@@ -49,6 +49,23 @@ int guarded(F&& f)
 }
 }  // namespace
 
+namespace
+{
+void peer_release(PeerLink& link)
+{
+    for (u32 g = 0; g < kPeerMaxWorld; g++)
+    {
+        if (!link.ptrs.buf[g]) continue;
+        if (g == link.rank) { if (link.created) cudaFree(link.ptrs.buf[g]); }
+        else cudaIpcCloseMemHandle(link.ptrs.buf[g]);
+        link.ptrs.buf[g] = nullptr;
+    }
+    cudaGetLastError();
+    link.created = link.attached = false;
+    link.bytes = 0;
+}
+}  // namespace
+
 struct wmh_engine
 {
     wmh_config cfg{};
@@ -85,6 +102,8 @@ struct wmh_engine
     double last_walk_kernel_ms = 0;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     DeviceBuffer<u32> small;           // misc tiny results
+    PeerLink peer;                     // exchange buffers of the box's ranks (wmh_peer_*)
+    CoalescedPlan* coalesced_plan = nullptr;   // scratch + CUDA graph of the coalesced deterministic pass
 
     LaunchCtx lc() { return LaunchCtx{stream, sm_count, &launches, &library_calls}; }
     void bind() const
@@ -99,6 +118,9 @@ struct wmh_engine
         cudaSetDevice(cfg.device);
         if (stream) cudaStreamSynchronize(stream);
         if (copy_stream) { cudaStreamSynchronize(copy_stream); cudaStreamDestroy(copy_stream); }
+        peer_release(peer);
+        g_alloc_stream = stream;
+        coalesced_plan_release(coalesced_plan);
         for (auto& e : ev) if (e) cudaEventDestroy(e);
         // buffers release in their destructors; the stream goes last
     }
@@ -227,6 +249,31 @@ void ensure_tails(wmh_engine& e)
     graph_enable_tails(lc, e.g);
 }
 
+// Exchange buffer a generate pass needs: MH node2vec shares the sampler init values, 2 bytes per edge.
+u64 peer_bytes_needed(const wmh_engine& e)
+{
+    if (e.cfg.world <= 1 || !needs_memo(e)) return 0;
+    return kPeerFlagBytes + 2 * ((e.g.m + 63) / 64 * 64 + 64);
+}
+
+bool peer_usable(const wmh_engine& e)
+{
+    const u64 need = peer_bytes_needed(e);
+    return e.peer.attached && need != 0 && e.peer.bytes >= need && e.peer.world == e.cfg.world && e.peer.rank == e.cfg.rank;
+}
+
+// A barrier that gave up waiting leaves a mark in the own flag page: the peers are out of step (or gone).
+void peer_check(wmh_engine& e)
+{
+    u32 flag = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&flag, e.peer.own() + kPeerErrorOffset, 4, cudaMemcpyDeviceToHost, e.stream));
+    WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    if (!flag) return;
+    WHARF_CUDA(cudaMemsetAsync(e.peer.own() + kPeerErrorOffset, 0, 4, e.stream));
+    throw CudaError(cudaErrorLaunchTimeout, "peer barrier timed out after " + std::to_string(WMH_PEER_TIMEOUT_MS) +
+                                            " ms: the ranks did not issue the same sequence of generate calls");
+}
+
 // Deterministic bulk generation: the coalesced schedule pays ~6 small launches per position, the per-walker kernel
 // two random loads per step; the latter wins while descriptors + neighbours stay in the 126 MB L2.
 bool use_coalesced(const wmh_engine& e)
@@ -274,7 +321,7 @@ void generate_and_export(wmh_engine& e, u32* host_out)
     if (use_coalesced(e))
     {
         const u64 nl = e.n_local;
-        walks_generate_coalesced(lc, wp, e.host_draw.data(), e.d_steps.ptr, [&](u32 replica) { export_range((u64) replica * nl, nl); });
+        walks_generate_coalesced(lc, wp, e.host_draw.data(), e.d_steps.ptr, [&](u32 replica) { export_range((u64) replica * nl, nl); }, &e.coalesced_plan);
     }
     else
     {
@@ -321,22 +368,29 @@ void generate(wmh_engine& e, u32* host_out = nullptr)
         e.draw_wpv = wpv;
         e.draw_len = L;
     }
-    if (needs_memo(e))
-    {
-        if (e.g.tail) graph_aux_clear_caches(lc, e.g);   // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90)
-        else ensure_tails(e);
-    }
-    tr.mark("generate: draws+memo+filter");
+    if (needs_memo(e)) ensure_tails(e);                  // one-time switch of the pool layout
+    tr.mark("generate: draws+tails");
     WHARF_CUDA(cudaMemsetAsync(e.d_steps.ptr, 0, 8, e.stream));
     WHARF_CUDA(cudaEventRecord(e.ev[0], e.stream));
+    bool exchanged = false;
+    if (needs_memo(e))
+    {
+        graph_aux_clear_caches(lc, e.g);                 // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90)
+        if (peer_usable(e))
+        {
+            n2v_share_sampler_init(lc, walk_params(e), e.g.m, e.peer);
+            exchanged = true;
+        }
+    }
     if (host_out) generate_and_export(e, host_out);
-    else if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr, nullptr);
+    else if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr, nullptr, &e.coalesced_plan);
     else walks_generate(lc, walk_params(e), e.d_steps.ptr);
     WHARF_CUDA(cudaEventRecord(e.ev[1], e.stream));
     unsigned long long steps = 0;
     WHARF_CUDA(cudaMemcpyAsync(&steps, e.d_steps.ptr, 8, cudaMemcpyDeviceToHost, e.stream));
     WHARF_CUDA(cudaStreamSynchronize(e.stream));
     if (host_out) WHARF_CUDA(cudaStreamSynchronize(e.copy_stream));
+    if (exchanged) peer_check(e);
     float ms = 0;
     WHARF_CUDA(cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]));
     e.last_walk_kernel_ms = ms;
@@ -634,6 +688,7 @@ int wmh_destroy_index(wmh_engine* e)
         e->codes.release();
         e->codes_valid = false;
         e->walks.release();
+        coalesced_plan_release(e->coalesced_plan);
         e->min_pos.release();
         e->aff_ids.release();
         e->aff_pos.release();
@@ -1079,6 +1134,69 @@ int wmh_synchronize(wmh_engine* e)
         return (int) WMH_OK;
     });
 }
+
+int wmh_peer_create(wmh_engine* e, uint64_t bytes, unsigned char handle_out[WMH_PEER_HANDLE_BYTES])
+{
+    if (!e || !handle_out) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        e->bind();
+        if (e->cfg.world > kPeerMaxWorld) throw std::invalid_argument("peer memory supports up to 8 ranks (one box)");
+        if (bytes < kPeerFlagBytes + 64) throw std::invalid_argument("exchange buffer too small");
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        peer_release(e->peer);
+        e->peer = PeerLink{};
+        e->peer.world = e->cfg.world;
+        e->peer.rank = e->cfg.rank;
+        void* p = nullptr;
+        WHARF_CUDA(cudaMalloc(&p, bytes));                    // IPC handles need a plain allocation, not the stream-ordered pool
+        e->peer.ptrs.buf[e->peer.rank] = static_cast<u8*>(p);
+        e->peer.bytes = bytes;
+        e->peer.created = true;
+        WHARF_CUDA(cudaMemset(p, 0, bytes));
+        WHARF_CUDA(cudaDeviceSynchronize());
+        cudaIpcMemHandle_t h;
+        WHARF_CUDA(cudaIpcGetMemHandle(&h, p));
+        static_assert(sizeof(h) == WMH_PEER_HANDLE_BYTES, "CUDA IPC handle size");
+        std::memcpy(handle_out, &h, sizeof(h));
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_peer_attach(wmh_engine* e, const unsigned char* handles)
+{
+    if (!e || !handles) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        e->bind();
+        PeerLink& link = e->peer;
+        if (!link.created) throw std::invalid_argument("wmh_peer_create must be called first");
+        if (link.world != e->cfg.world || link.rank != e->cfg.rank) throw std::invalid_argument("rank/world changed since wmh_peer_create");
+        for (u32 g = 0; g < link.world; g++)
+        {
+            if (g == link.rank || link.ptrs.buf[g]) continue;
+            cudaIpcMemHandle_t h;
+            std::memcpy(&h, handles + (size_t) g * WMH_PEER_HANDLE_BYTES, sizeof(h));
+            void* p = nullptr;
+            WHARF_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+            link.ptrs.buf[g] = static_cast<u8*>(p);
+        }
+        link.attached = true;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_peer_detach(wmh_engine* e)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    return guarded([&] {
+        e->bind();
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        peer_release(e->peer);
+        return (int) WMH_OK;
+    });
+}
+
+uint64_t wmh_peer_bytes_needed(const wmh_engine* e) { return e ? peer_bytes_needed(*e) : 0; }
+uint64_t wmh_peer_exchanges(const wmh_engine* e) { return e ? e->peer.exchanges : 0; }
 
 int wmh_trim_memory(int device)
 {

@@ -107,6 +107,30 @@ struct PreparedBatch
     Scratch<u64> slice;              // n_src+1: batch slice of each source in keys
 };
 
+// ------------------------------------------------------------------------------------------------
+// Peer memory between the ranks of one box (include/wharfmh_b200.h, wmh_peer_*): every rank owns one exchange
+// buffer; buf[g] is rank g's buffer mapped into this process (CUDA IPC over NVLink), buf[rank] the own one.
+// Layout: a flag page (arrival epochs written by the peers, an error word), then the payload.
+// ------------------------------------------------------------------------------------------------
+constexpr u32 kPeerMaxWorld = WMH_PEER_MAX_WORLD;
+constexpr u64 kPeerFlagBytes = 4096;
+constexpr u64 kPeerErrorOffset = 1024;   // u32 in the own flag page: a barrier gave up waiting
+struct PeerPtrs { u8* buf[kPeerMaxWorld]; };
+struct PeerLink
+{
+    u32 world = 1, rank = 0;
+    PeerPtrs ptrs{};
+    u64 bytes = 0;                   // size of every rank's buffer (flag page included)
+    u64 epoch = 0;                   // barriers passed
+    u64 exchanges = 0;               // generate passes that used the exchange
+    bool created = false, attached = false;
+    u8* own() const { return ptrs.buf[rank]; }
+    u64 payload_bytes() const { return bytes > kPeerFlagBytes ? bytes - kPeerFlagBytes : 0; }
+};
+// All ranks meet: every kernel enqueued before it on every rank's stream has completed (and its peer stores are
+// visible) before any kernel enqueued after it starts.
+void peer_barrier(const LaunchCtx& lc, PeerLink& link);
+
 // ---- graph kernels (kernels_graph.cu) -------------------------------------------------------------
 void graph_build_desc(const LaunchCtx& lc, const u64* d_offsets_n, u64 n, u64 m, RowDesc* d_desc);
 void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, bool drop_self_loops, u64 n,
@@ -144,14 +168,20 @@ struct WalkParams
     u64 seed = 0;
 };
 void walks_generate(const LaunchCtx& lc, const WalkParams& wp, unsigned long long* d_steps);
+// MH node2vec with peers attached: the first-touch sampler value of every state (cur, prev) - a pure function of
+// the replicated graph - is computed by one rank per state and stored into every peer's exchange buffer, then
+// copied into the aux tails, so the walk kernel starts with warm caches on every rank.  Payload: 2 bytes per edge.
+void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, PeerLink& link);
 void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affected, const u32* d_positions, u64 count,
                   unsigned long long* d_steps);
 // Deterministic mode only: step-synchronous generation that advances walkers standing on the same vertex once
 // (kernels_coalesced.cu).  host_draw = X[wpv][L] on the host.
 // after_replica(r), when given, is called once replica r's column block [r * n_local, (r + 1) * n_local) has been
 // fully enqueued on lc.stream.
+struct CoalescedPlan;                       // scratch + captured CUDA graph of one generate pass (kernels_coalesced.cu)
+void coalesced_plan_release(CoalescedPlan*& plan);
 void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
-                              const std::function<void(u32)>& after_replica);
+                              const std::function<void(u32)>& after_replica, CoalescedPlan** plan_slot);
 // Bulk generation of the local walks [first, first + count) with one walker per thread.
 void walks_generate_range(const LaunchCtx& lc, const WalkParams& wp, u64 first, u64 count, unsigned long long* d_steps);
 // min_pos[w] = first position whose vertex is in the touched bitmap (kNoPos when none).

@@ -237,33 +237,77 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
 }
 }  // namespace
 
-void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
-                              const std::function<void(u32)>& after_replica)
+// Scratch of the schedule plus, when no per-replica callback is wanted, the whole pass as one CUDA graph: ~2700
+// kernel launches per generate (scale-25: most of them a few microseconds long) replayed without host work.
+struct CoalescedPlan
 {
-    if (wp.w_local == 0) return;
-    const u32 nl = wp.n_local, L = wp.L;
-    const u32 words = (u32) ((wp.n + 31) / 32);
-    Scratch<u32> cls(lc.stream, nl), cv_a(lc.stream, (u64) nl + 1), cv_b(lc.stream, (u64) nl + 1);
-    Scratch<u32> rec(lc.stream, ((u64) nl + 1) * kMaxRec);
-    Scratch<u32> bitmap(lc.stream, words), word_rank(lc.stream, (u64) words + 1), counts(lc.stream, 2);
-    Scratch<uint2> table(lc.stream, words);
-    WHARF_CUDA(cudaMemsetAsync(bitmap.ptr, 0, (u64) words * 4, lc.stream));
-
+    Scratch<u32> cls, cv_a, cv_b, rec, bitmap, word_rank, counts;
+    Scratch<uint2> table;
+    Scratch<u8> temp;
     size_t temp_bytes = 0;
+    u32 n_local = 0, words = 0;
+    cudaGraphExec_t exec = nullptr;
+    u64 graph_launches = 0, graph_lib_calls = 0;
+    struct Key
     {
-        cub::CountingInputIterator<u32> iota(0);
-        cub::TransformInputIterator<u32, PopcountOf, cub::CountingInputIterator<u32>> pops(iota, PopcountOf{bitmap.ptr, words});
-        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, pops, word_rank.ptr, (int) (words + 1), lc.stream));
+        const void *desc, *pool, *walks, *steps;
+        u64 n, w_local, draw_hash;
+        u32 n_local, wpv, L, rank, world;
+        bool operator==(const Key& o) const
+        {
+            return desc == o.desc && pool == o.pool && walks == o.walks && steps == o.steps && n == o.n && w_local == o.w_local &&
+                   draw_hash == o.draw_hash && n_local == o.n_local && wpv == o.wpv && L == o.L && rank == o.rank && world == o.world;
+        }
+    } key{};
+    void drop_graph()
+    {
+        if (exec) cudaGraphExecDestroy(exec);
+        exec = nullptr;
     }
-    Scratch<u8> temp(lc.stream, temp_bytes);
+    ~CoalescedPlan() { drop_graph(); }
+};
 
-    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock), cls.ptr, rec.ptr, bitmap.ptr,
-                 word_rank.ptr, table.ptr, temp.ptr, temp_bytes, d_steps};
+void coalesced_plan_release(CoalescedPlan*& plan)
+{
+    delete plan;
+    plan = nullptr;
+}
+
+namespace
+{
+void plan_buffers(CoalescedPlan& pl, const LaunchCtx& lc, u32 nl, u32 words)
+{
+    if (pl.n_local == nl && pl.words == words && pl.cls.ptr) return;
+    pl.drop_graph();
+    pl.cls.allocate(lc.stream, nl);
+    pl.cv_a.allocate(lc.stream, (u64) nl + 1);
+    pl.cv_b.allocate(lc.stream, (u64) nl + 1);
+    pl.rec.allocate(lc.stream, ((u64) nl + 1) * kMaxRec);
+    pl.bitmap.allocate(lc.stream, words);
+    pl.word_rank.allocate(lc.stream, (u64) words + 1);
+    pl.counts.allocate(lc.stream, 2);
+    pl.table.allocate(lc.stream, words);
+    cub::CountingInputIterator<u32> iota(0);
+    cub::TransformInputIterator<u32, PopcountOf, cub::CountingInputIterator<u32>> pops(iota, PopcountOf{pl.bitmap.ptr, words});
+    pl.temp_bytes = 0;
+    WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, pl.temp_bytes, pops, pl.word_rank.ptr, (int) (words + 1), lc.stream));
+    pl.temp.allocate(lc.stream, pl.temp_bytes);
+    pl.n_local = nl;
+    pl.words = words;
+}
+
+void enqueue_pass(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
+                  const std::function<void(u32)>& after_replica)
+{
+    const u32 nl = wp.n_local, L = wp.L, words = pl.words;
+    WHARF_CUDA(cudaMemsetAsync(pl.bitmap.ptr, 0, (u64) words * 4, lc.stream));
+    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock), pl.cls.ptr, pl.rec.ptr, pl.bitmap.ptr,
+                 pl.word_rank.ptr, pl.table.ptr, pl.temp.ptr, pl.temp_bytes, d_steps};
     for (u32 r = 0; r < wp.wpv; r++)
     {
-        u32 *cv = cv_a.ptr, *cv_next = cv_b.ptr, *nc = counts.ptr, *nc_next = counts.ptr + 1;
+        u32 *cv = pl.cv_a.ptr, *cv_next = pl.cv_b.ptr, *nc = pl.counts.ptr, *nc_next = pl.counts.ptr + 1;
         u32* col = wp.walks + (u64) r * nl;                       // column block of the replica in every corpus row
-        coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(cls.ptr, cv, col, nl, wp.rank, wp.world, nc);
+        coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(pl.cls.ptr, cv, col, nl, wp.rank, wp.world, nc);
         lc.count();
         for (u32 a = 0; a < L;)
         {
@@ -286,6 +330,67 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
         WHARF_CUDA(cudaGetLastError());
         if (after_replica) after_replica(r);
     }
+}
+
+bool graphs_enabled()
+{
+    static const bool on = [] { const char* e = std::getenv("WHARF_GRAPH"); return !e || std::atoi(e) != 0; }();
+    return on;
+}
+}  // namespace
+
+void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
+                              const std::function<void(u32)>& after_replica, CoalescedPlan** plan_slot)
+{
+    if (wp.w_local == 0) return;
+    const u32 words = (u32) ((wp.n + 31) / 32);
+    CoalescedPlan local;
+    CoalescedPlan* pl = &local;
+    if (plan_slot)
+    {
+        if (!*plan_slot) *plan_slot = new CoalescedPlan();
+        pl = *plan_slot;
+    }
+    plan_buffers(*pl, lc, wp.n_local, words);
+    if (after_replica || !plan_slot || !graphs_enabled())
+    {
+        enqueue_pass(lc, wp, host_draw, d_steps, *pl, after_replica);
+        return;
+    }
+    u64 draw_hash = 1469598103934665603ull;
+    for (u64 i = 0; i < (u64) wp.wpv * wp.L; i++) draw_hash = (draw_hash ^ host_draw[i]) * 1099511628211ull;
+    const CoalescedPlan::Key key{wp.desc, wp.pool, wp.walks, d_steps, wp.n, wp.w_local, draw_hash, wp.n_local, wp.wpv, wp.L, wp.rank, wp.world};
+    if (!pl->exec || !(pl->key == key))
+    {
+        pl->drop_graph();
+        u64 launches = 0, lib_calls = 0;
+        LaunchCtx cap = lc;
+        cap.launches = &launches;
+        cap.library_calls = &lib_calls;
+        cudaGraph_t graph = nullptr;
+        WHARF_CUDA(cudaStreamBeginCapture(lc.stream, cudaStreamCaptureModeThreadLocal));
+        try
+        {
+            enqueue_pass(cap, wp, host_draw, d_steps, *pl, nullptr);
+        }
+        catch (...)
+        {
+            cudaStreamEndCapture(lc.stream, &graph);
+            if (graph) cudaGraphDestroy(graph);
+            cudaGetLastError();
+            throw;
+        }
+        WHARF_CUDA(cudaStreamEndCapture(lc.stream, &graph));
+        const cudaError_t err = cudaGraphInstantiate(&pl->exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (err != cudaSuccess) { pl->exec = nullptr; WHARF_CUDA(err); }
+        pl->key = key;
+        pl->graph_launches = launches;
+        pl->graph_lib_calls = lib_calls;
+    }
+    WHARF_CUDA(cudaGraphLaunch(pl->exec, lc.stream));
+    lc.count(pl->graph_launches);
+    lc.count_lib(pl->graph_lib_calls);
 }
 
 }  // namespace wharf

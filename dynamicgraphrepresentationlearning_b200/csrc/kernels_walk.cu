@@ -10,9 +10,11 @@
 #include "engine.hpp"
 #include "rng.cuh"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 
+#include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
@@ -479,6 +481,160 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkPar
     block_add_u64(steps_out, steps);
 }
 
+// ---- cooperative sampler init over peer memory (MH node2vec, world > 1) ----------------------------------
+//
+// The init value of the sampler of state (cur, prev) is a pure function of the replicated graph, so the box computes
+// each one once: states are numbered in row order (state e = eoff[prev] + slot of cur in the row of prev), rank g
+// owns the states of the vertex range [split[g], split[g + 1]) (equal edge counts), and its kernel stores the 16-bit
+// cache words straight into the exchange buffer of every peer (32-byte vector stores over NVLink: 16 consecutive
+// states) and into its own aux tails.  After the barrier every rank copies the words it received into its tails.
+
+struct DegreeOf
+{
+    const RowDesc* desc;
+    u64 n;
+    __device__ u32 operator()(u32 v) const { return v < n ? desc[v].degree : 0u; }
+};
+
+// split[g] = first vertex whose state offset is >= g * m / world (g = 0..world), so hub rows are never cut.
+__global__ void share_splits_kernel(const u32* __restrict__ eoff, u32 n, u32 world, u32* __restrict__ split)
+{
+    const u32 g = threadIdx.x;
+    if (g > world) return;
+    const u32 m = eoff[n];
+    const u32 target = (u32) ((u64) m * g / world);
+    u32 lo = 0, hi = n;                                  // lower_bound over eoff[0..n)
+    while (lo < hi)
+    {
+        const u32 mid = (lo + hi) >> 1;
+        if (eoff[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    split[g] = g == world ? n : lo;
+}
+
+constexpr u32 kShareChunk = 64;      // states per warp round: four 8-lane groups x 16 consecutive states
+
+__global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParams p, const u32* __restrict__ eoff, const u32* __restrict__ split,
+                                                                     PeerPtrs peers, u32 world, u32 rank)
+{
+    const u32 lane = threadIdx.x & 31, sub = lane & 7, group = lane >> 3;
+    const u32 vlo = split[rank], vhi = split[rank + 1];
+    if (vlo >= vhi) return;
+    const u64 elo = eoff[vlo], ehi = eoff[vhi];
+    const u64 base = elo & ~(u64) (kShareChunk - 1);
+    const u64 warps = ((u64) gridDim.x * kWalkBlock) >> 5;
+    unsigned short* const remote = (sub < world && sub != rank) ? reinterpret_cast<unsigned short*>(peers.buf[sub] + kPeerFlagBytes) : nullptr;
+    for (u64 chunk = ((u64) blockIdx.x * kWalkBlock + threadIdx.x) >> 5; base + chunk * kShareChunk < ehi; chunk += warps)
+    {
+        const u64 e0 = base + chunk * kShareChunk + group * 16;          // this group's 16 states
+        // row of the group's first state: largest v in [vlo, vhi) with eoff[v] <= max(e0, elo)
+        u32 v = vlo;
+        {
+            const u64 key = e0 < elo ? elo : e0;
+            u32 lo = vlo, hi = vhi;                                      // upper_bound - 1
+            while (lo < hi)
+            {
+                const u32 mid = (lo + hi) >> 1;
+                if (__ldg(eoff + mid) <= key) lo = mid + 1; else hi = mid;
+            }
+            v = lo > vlo ? lo - 1 : vlo;
+        }
+        u32 next_off = v + 1 <= vhi ? __ldg(eoff + v + 1) : 0xFFFFFFFFu;
+        RowDesc dprev = load_desc(p.desc, v);
+        u32 row_off = __ldg(eoff + v);
+        u32 acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+        for (u32 r = 0; r < 16; r++)
+        {
+            const u64 e = e0 + r;
+            const bool mine = e >= elo && e < ehi;
+            u32 cur = 0, slot = 0;
+            RowDesc d{0, 0};
+            if (mine)
+            {
+                while (e >= next_off)                                    // next row (skips empty rows)
+                {
+                    ++v;
+                    row_off = next_off;
+                    next_off = __ldg(eoff + v + 1);
+                    dprev = load_desc(p.desc, v);
+                }
+                slot = (u32) (e - row_off);
+                cur = __ldg(p.pool + dprev.begin + slot);
+                d = load_desc(p.desc, cur);
+            }
+            const bool has = mine && d.degree != 0;                      // a walker on a sink never samples
+            InitValue iv{kClassFar, 0, 0};
+            if (p.init_strategy == WMH_INIT_WEIGHT) iv = n2v_init_weight_group(p, sub, has, cur, d, v, dprev);
+            else
+            {
+                if (has && sub == 0) iv = n2v_init_serial(p, cur, d, v, dprev);
+                const int from = (int) (lane & ~7u);
+                iv = InitValue{__shfl_sync(0xffffffffu, iv.cls, from), __shfl_sync(0xffffffffu, iv.slot, from), __shfl_sync(0xffffffffu, iv.draw, from)};
+            }
+            const u32 word = has ? cache_encode(iv, d.degree) : 0u;
+            acc[r >> 1] |= word << ((r & 1) * 16);
+            if (mine && sub == 0)
+                __stcg(reinterpret_cast<unsigned short*>(p.pool_rw + dprev.begin + dprev.degree + slot), (unsigned short) word);   // own tail, low half
+        }
+        if (remote)
+        {
+            if (e0 >= elo && e0 + 16 <= ehi)                             // whole window owned: one sector
+            {
+                uint4* dst = reinterpret_cast<uint4*>(remote + e0);
+                dst[0] = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+                dst[1] = make_uint4(acc[4], acc[5], acc[6], acc[7]);
+            }
+            else
+            {
+                for (u32 r = 0; r < 16; r++)
+                    if (e0 + r >= elo && e0 + r < ehi) remote[e0 + r] = (unsigned short) (acc[r >> 1] >> ((r & 1) * 16));
+            }
+        }
+    }
+}
+
+// Eight lanes per row: tails of the rows other ranks computed <- the words they stored into the own exchange buffer.
+__global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
+                                                               const u32* __restrict__ split, const unsigned short* __restrict__ received, u32 n, u32 rank)
+{
+    const u64 t = (u64) blockIdx.x * 256 + threadIdx.x;
+    const u32 v = (u32) (t >> 3), sub = threadIdx.x & 7;
+    if (v >= n || (v >= split[rank] && v < split[rank + 1])) return;
+    const RowDesc d = load_desc(desc, v);
+    const unsigned short* src = received + __ldg(eoff + v);
+    unsigned short* cache = reinterpret_cast<unsigned short*>(pool + d.begin + d.degree);      // low half of aux word i = cache[2 i]
+    for (u32 i = sub; i < d.degree; i += 8) cache[2 * i] = __ldcs(src + i);
+}
+
+// Flag barrier in peer memory: lane g tells rank g "rank `rank` reached epoch", then waits for rank g's word in the
+// own flag page.  Kernel boundaries order the data: the stores of every kernel enqueued before this one are performed
+// before the release store, and kernels enqueued after it start after the acquire loads saw every peer.
+__global__ void peer_barrier_kernel(PeerPtrs peers, u32 world, u32 rank, u64 epoch, u64 timeout_ns)
+{
+    const u32 g = threadIdx.x;
+    if (g >= world) return;
+    __threadfence_system();
+    unsigned long long* there = reinterpret_cast<unsigned long long*>(peers.buf[g]) + rank;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(there), "l"(epoch) : "memory");
+    const unsigned long long* here = reinterpret_cast<const unsigned long long*>(peers.buf[rank]) + g;
+    unsigned long long t0, now, seen;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;)
+    {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(here) : "memory");
+        if (seen >= epoch) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > timeout_ns)
+        {
+            *reinterpret_cast<u32*>(peers.buf[rank] + kPeerErrorOffset) = 1u;
+            break;
+        }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
 // ---- corpus scan: earliest position standing on a touched vertex (MapOfChanges, wharfmh.h:519-537) ----
 __global__ void __launch_bounds__(256) scan_touched_kernel(const u32* __restrict__ walks, u64 w_local, u32 L,
                                                             const u32* __restrict__ bitmap, u32* __restrict__ min_pos)
@@ -728,6 +884,42 @@ void fill_u32(const LaunchCtx& lc, u32* d, u64 count, u32 value)
     fill_u32_kernel<<<grid_for(count, 256, 8, lc.sm_count), 256, 0, lc.stream>>>(d, count, value);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
+}
+
+void peer_barrier(const LaunchCtx& lc, PeerLink& link)
+{
+    ++link.epoch;
+    peer_barrier_kernel<<<1, 32, 0, lc.stream>>>(link.ptrs, link.world, link.rank, link.epoch, (u64) WMH_PEER_TIMEOUT_MS * 1000000ull);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, PeerLink& link)
+{
+    const u32 n = (u32) wp.n;
+    Scratch<u32> eoff(lc.stream, (u64) n + 1), split(lc.stream, kPeerMaxWorld + 1);
+    {
+        cub::CountingInputIterator<u32> iota(0);
+        cub::TransformInputIterator<u32, DegreeOf, cub::CountingInputIterator<u32>> degrees(iota, DegreeOf{wp.desc, wp.n});
+        size_t temp_bytes = 0;
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, degrees, eoff.ptr, (int) (n + 1), lc.stream));
+        Scratch<u8> temp(lc.stream, temp_bytes);
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(temp.ptr, temp_bytes, degrees, eoff.ptr, (int) (n + 1), lc.stream));
+        lc.count_lib();
+    }
+    share_splits_kernel<<<1, 32, 0, lc.stream>>>(eoff.ptr, n, link.world, split.ptr);
+    const DevWalkParams p = to_dev(wp);
+    const u64 chunks = (m / link.world + kShareChunk) / kShareChunk + 2;
+    const unsigned grid = (unsigned) std::min<u64>(div_up(chunks * 32, kWalkBlock), (u64) lc.sm_count * 8);
+    n2v_share_init_kernel<<<grid, kWalkBlock, 0, lc.stream>>>(p, eoff.ptr, split.ptr, link.ptrs, link.world, link.rank);
+    lc.count(2);
+    peer_barrier(lc, link);                                    // every rank's words have arrived
+    n2v_share_import_kernel<<<div_up((u64) n * 8, 256), 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, split.ptr,
+                                                                             reinterpret_cast<const unsigned short*>(link.own() + kPeerFlagBytes), n, link.rank);
+    lc.count();
+    peer_barrier(lc, link);                                    // nobody overwrites a buffer that is still being read
+    WHARF_CUDA(cudaGetLastError());
+    ++link.exchanges;
 }
 
 }  // namespace wharf

@@ -18,6 +18,26 @@ import torch.distributed as dist
 from .wharfmh import Config, WharfMH
 
 
+def connect_peers(engine, group=None, slack: float = 1.25) -> bool:
+    """Gives the ranks of one box a window into each other's memory (include/wharfmh_b200.h, wmh_peer_*): every rank
+    allocates an exchange buffer, the 64-byte CUDA IPC handles travel through torch.distributed (host plumbing), and
+    every rank maps the others'.  From then on work that is a pure function of the replicated graph (node2vec sampler
+    init values) is computed once per box and stored into the peers over NVLink by the kernel that computes it.
+    Returns False when the engine's configuration has nothing to exchange.  Collective: call it on every rank."""
+    need = engine.peer_bytes_needed()
+    sizes = [None] * dist.get_world_size(group)
+    dist.all_gather_object(sizes, need, group=group)
+    if max(sizes) == 0:
+        return False
+    nbytes = int(max(sizes) * slack) + (1 << 20)        # room for the graph to grow by edge batches
+    handle = engine.peer_create(nbytes)
+    handles = [None] * dist.get_world_size(group)
+    dist.all_gather_object(handles, handle, group=group)   # also orders every create before any attach
+    engine.peer_attach(handles)
+    dist.barrier(group=group)
+    return True
+
+
 class ShardedWharfMH:
     """dygrl::WharfMH over `world` ranks.  `engine_factory(config) -> engine` builds the per-rank engine (default:
     the CUDA engine over the given host CSR); tests inject a stand-in to exercise the exchange logic on gloo."""
@@ -36,6 +56,8 @@ class ShardedWharfMH:
         self.device = torch.device(f"cuda:{cfg.device}") if self._on_gpu else torch.device("cpu")
         if engine_factory is None:
             self.engine = WharfMH(graph_vertices, graph_edges, offsets, edges, config=cfg)
+            if self._on_gpu and 1 < self.world <= 8:
+                connect_peers(self.engine, group)
         else:
             self.engine = engine_factory(cfg)
 

@@ -301,6 +301,30 @@ class WharfMH:
     def synchronize(self) -> None:
         check(self._lib.wmh_synchronize(self._h))
 
+    # -- peer memory between the ranks of one box (include/wharfmh_b200.h, wmh_peer_*) ------------------
+    def peer_bytes_needed(self) -> int:
+        return int(self._lib.wmh_peer_bytes_needed(self._h))
+
+    def peer_create(self, nbytes: int) -> bytes:
+        """Allocates this rank's exchange buffer; returns its 64-byte CUDA IPC handle."""
+        handle = (C.c_ubyte * 64)()
+        check(self._lib.wmh_peer_create(self._h, int(nbytes), handle))
+        return bytes(handle)
+
+    def peer_attach(self, handles: list[bytes]) -> None:
+        """Maps the exchange buffers of all ranks (handles in rank order, 64 bytes each)."""
+        blob = b"".join(handles)
+        if len(blob) != 64 * len(handles):
+            raise ValueError("every handle must be 64 bytes")
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        check(self._lib.wmh_peer_attach(self._h, buf))
+
+    def peer_detach(self) -> None:
+        check(self._lib.wmh_peer_detach(self._h))
+
+    def peer_exchanges(self) -> int:
+        return int(self._lib.wmh_peer_exchanges(self._h))
+
 
 def trim_memory(device: int = 0) -> None:
     """Returns the blocks cached by destroyed engines / finished batches to the driver (wmh_trim_memory)."""

@@ -252,6 +252,36 @@ WMH_API int      wmh_synchronize(wmh_engine* e);
  * never returned either).  This hands every unused block back to the driver. */
 WMH_API int      wmh_trim_memory(int device);
 
+/* ---- peer memory between the ranks of one box (no counterpart in the single-process reference) -- */
+
+/* With config.world > 1 every rank holds a replica of the graph and owns the walks whose start vertex satisfies
+ * start % world == rank.  Work that is a pure function of the replicated graph - the first-touch value of every
+ * node2vec sampler (SamplerManager, graph/vertex.h:12 / metropolis_hastings_sampler.h:69-108) and, in
+ * deterministic mode, the step of every class of walkers - is then computed ONCE per box instead of once per
+ * rank: each rank computes a slice and its kernel stores the results straight into the exchange buffers of
+ * all its peers over NVLink (peer-mapped device memory, no collective library on the data path).
+ *
+ *   wmh_peer_create  allocates this rank's exchange buffer (device memory, zeroed) and returns its 64-byte
+ *                    CUDA IPC handle; the caller distributes the handles through any host channel
+ *                    (torch.distributed all_gather, MPI, a file).
+ *   wmh_peer_attach  maps the buffers of all `config.world` ranks: handles = world x 64 bytes, in rank order
+ *                    (the own slot is ignored).  Every rank must have returned from wmh_peer_create before any
+ *                    rank attaches, and all ranks must issue the same sequence of generate calls afterwards
+ *                    (the kernels meet at a flag barrier in peer memory; a rank that never arrives makes the
+ *                    others fail with WMH_ERR_CUDA after WMH_PEER_TIMEOUT_MS instead of hanging).
+ *   wmh_peer_detach  unmaps the peers and frees the buffer (also done by wmh_destroy).
+ * Results never depend on whether peers are attached: the corpus is bit-identical either way. */
+#define WMH_PEER_HANDLE_BYTES 64
+#define WMH_PEER_MAX_WORLD 8
+#define WMH_PEER_TIMEOUT_MS 4000
+WMH_API int wmh_peer_create(wmh_engine* e, uint64_t bytes, unsigned char handle_out[WMH_PEER_HANDLE_BYTES]);
+WMH_API int wmh_peer_attach(wmh_engine* e, const unsigned char* handles);
+WMH_API int wmh_peer_detach(wmh_engine* e);
+/* Bytes of exchange buffer the current graph and config need (0 when no exchange applies). */
+WMH_API uint64_t wmh_peer_bytes_needed(const wmh_engine* e);
+/* Number of generate passes that used the peer exchange so far (0: every pass ran stand-alone). */
+WMH_API uint64_t wmh_peer_exchanges(const wmh_engine* e);
+
 /* ---- synthetic input (utils/utility.h:55-146 generate_batch_of_edges, rmat_util.h) --------------- */
 
 /* Device restatement of utility::generate_batch_of_edges: RMAT(a,b,c) edges over 2^(log2_up(vertices)-1)

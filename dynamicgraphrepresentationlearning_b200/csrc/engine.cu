@@ -381,6 +381,16 @@ void generate(wmh_engine& e, u32* host_out = nullptr)
             n2v_share_sampler_init(lc, walk_params(e), e.g.m, e.peer);
             exchanged = true;
         }
+        else if (e.cfg.world == 1 && std::getenv("WHARF_EAGER_INIT") && std::atoi(std::getenv("WHARF_EAGER_INIT")))
+        {
+            // tuning aid: the same bulk kernel on one rank (every state initialised up front instead of at first touch)
+            Scratch<u8> flags(e.stream, kPeerFlagBytes);
+            WHARF_CUDA(cudaMemsetAsync(flags.ptr, 0, kPeerFlagBytes, e.stream));
+            PeerLink solo;
+            solo.ptrs.buf[0] = flags.ptr;
+            solo.bytes = kPeerFlagBytes;
+            n2v_share_sampler_init(lc, walk_params(e), e.g.m, solo);
+        }
     }
     if (host_out) generate_and_export(e, host_out);
     else if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr, nullptr, &e.coalesced_plan);

@@ -35,6 +35,7 @@ namespace wharf
 namespace
 {
 constexpr int kBlock = 256;
+constexpr u32 kEmitWalkers = 4;     // walkers per emit thread
 constexpr u32 kMaxRec = 8;          // words per class record: 7 vertices + next class = one 32-byte sector
 
 struct SegDraws { u64 x[kMaxRec]; };
@@ -176,19 +177,33 @@ template <u32 R, bool kRelabel>
 __global__ void __launch_bounds__(kBlock) coalesced_emit_kernel(u32* __restrict__ cls, const u32* __restrict__ rec, u32* __restrict__ first_row,
                                                                 u64 row_stride, u32 stored, u32 n_local, unsigned long long* __restrict__ steps_out)
 {
-    const u32 i = blockIdx.x * kBlock + threadIdx.x;
-    u32 moved = 0;
-    if (i < n_local)
+    // kEmitWalkers walkers per thread, kBlock apart (every access stays coalesced): the class loads of all of them are
+    // in flight before the first record gather, the gathers before the first store
+    const u32 i0 = blockIdx.x * (kBlock * kEmitWalkers) + threadIdx.x;
+    u32 c[kEmitWalkers];
+#pragma unroll
+    for (u32 v = 0; v < kEmitWalkers; v++)
     {
-        u32 t[R];
-        load_record<R>(rec, __ldcs(cls + i), t);
-        if (kRelabel) __stcs(cls + i, t[R - 1]);
+        const u32 i = i0 + v * kBlock;
+        c[v] = i < n_local ? __ldcs(cls + i) : 0xFFFFFFFFu;
+    }
+    u32 t[kEmitWalkers][R];
+#pragma unroll
+    for (u32 v = 0; v < kEmitWalkers; v++)
+        if (c[v] != 0xFFFFFFFFu) load_record<R>(rec, c[v], t[v]);
+    u32 moved = 0;
+#pragma unroll
+    for (u32 v = 0; v < kEmitWalkers; v++)
+    {
+        const u32 i = i0 + v * kBlock;
+        if (c[v] == 0xFFFFFFFFu) continue;
+        if (kRelabel) __stcs(cls + i, t[v][R - 1]);
         u32* out = first_row + i;
 #pragma unroll
         for (u32 j = 0; j < R - 1; j++)
         {
-            if (j < stored) __stcs(out + (u64) j * row_stride, t[j]);
-            moved += t[j] != kNoVertex;
+            if (j < stored) __stcs(out + (u64) j * row_stride, t[v][j]);
+            moved += t[v][j] != kNoVertex;
         }
     }
     block_add_u64(steps_out, moved);
@@ -202,7 +217,7 @@ struct SegmentCtx
     const LaunchCtx& lc;
     const WalkParams& wp;
     u32 words;
-    unsigned walker_grid, class_grid, word_grid;
+    unsigned walker_grid, emit_grid, class_grid, word_grid;
     u32 *cls, *rec, *bitmap, *word_rank;
     uint2* table;
     void* scan_temp;
@@ -226,12 +241,12 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
         lc.count_lib();
         coalesced_expand_kernel<<<s.word_grid, kBlock, 0, lc.stream>>>(s.bitmap, s.word_rank, s.words, s.table, cv_next, nc_next);
         coalesced_relabel_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.rec, s.table, s.word_rank, s.words, nc);
-        coalesced_emit_kernel<R, true><<<s.walker_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
+        coalesced_emit_kernel<R, true><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
         lc.count(3);
     }
     else
     {
-        coalesced_emit_kernel<R, false><<<s.walker_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
+        coalesced_emit_kernel<R, false><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
         lc.count();
     }
 }
@@ -301,7 +316,7 @@ void enqueue_pass(const LaunchCtx& lc, const WalkParams& wp, const u64* host_dra
 {
     const u32 nl = wp.n_local, L = wp.L, words = pl.words;
     WHARF_CUDA(cudaMemsetAsync(pl.bitmap.ptr, 0, (u64) words * 4, lc.stream));
-    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock), pl.cls.ptr, pl.rec.ptr, pl.bitmap.ptr,
+    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), div_up(nl, kBlock * kEmitWalkers), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock), pl.cls.ptr, pl.rec.ptr, pl.bitmap.ptr,
                  pl.word_rank.ptr, pl.table.ptr, pl.temp.ptr, pl.temp_bytes, d_steps};
     for (u32 r = 0; r < wp.wpv; r++)
     {

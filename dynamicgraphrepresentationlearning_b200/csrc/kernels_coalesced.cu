@@ -24,11 +24,15 @@
 // The corpus is bit-identical to the one-walker-per-thread kernel (tests/test_gpu_parity.py).
 #include "engine.hpp"
 
+#include <cub/block/block_reduce.cuh>
+#include <cub/block/block_scan.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
 
 #include <algorithm>
+#include <cstdlib>
+#include <vector>
 
 namespace wharf
 {
@@ -123,16 +127,108 @@ struct PopcountOf
     __device__ u32 operator()(u32 w) const { return w < words ? (u32) __popc(bitmap[w]) : 0u; }
 };
 
-// One thread per bitmap word: the occupied vertices, in ascending order, are the classes of the next segment.
-// Leaves table[w] = (rank of the word's first occupied vertex, the word's bits) for relabel and clears the bitmap.
-__global__ void __launch_bounds__(kBlock) coalesced_expand_kernel(u32* __restrict__ bitmap, const u32* __restrict__ word_rank, u32 words,
+// Ranking of the occupied vertices, two launches over the bitmap (n / 32 words):
+//   tile_counts  one block per tile of kTileWords words: number of occupied vertices in the tile;
+//   expand       the block sums the counts of the tiles before its own (at most kMaxTiles of them), scans its tile and,
+//                for every word, writes table[w] = (rank of the word's first occupied vertex, the word's bits), lays
+//                down the vertices of the next classes (ascending: the occupied vertices) and clears the word.
+// table[words] = (number of occupied vertices, 0): the class shared by every walker that stopped.
+constexpr u32 kWordsPerThread = 4;
+constexpr u32 kTileWords = kBlock * kWordsPerThread;
+constexpr u32 kMaxTiles = 4096;      // larger bitmaps (n > 134 M vertices) take the library scan
+
+__global__ void __launch_bounds__(kBlock) coalesced_tile_counts_kernel(const u32* __restrict__ bitmap, u32 words, u32* __restrict__ tile_count)
+{
+    using BlockReduce = cub::BlockReduce<u32, kBlock>;
+    __shared__ typename BlockReduce::TempStorage temp;
+    const u32 w0 = blockIdx.x * kTileWords + threadIdx.x * kWordsPerThread;
+    u32 c = 0;
+    if (w0 + kWordsPerThread <= words)
+    {
+#pragma unroll
+        for (u32 q = 0; q < kWordsPerThread / 4; q++)
+        {
+            const uint4 b = reinterpret_cast<const uint4*>(bitmap + w0)[q];
+            c += __popc(b.x) + __popc(b.y) + __popc(b.z) + __popc(b.w);
+        }
+    }
+    else
+        for (u32 w = w0; w < words; w++) c += __popc(bitmap[w]);
+    const u32 sum = BlockReduce(temp).Sum(c);
+    if (threadIdx.x == 0) tile_count[blockIdx.x] = sum;
+}
+
+__global__ void __launch_bounds__(kBlock) coalesced_expand_kernel(u32* __restrict__ bitmap, const u32* __restrict__ tile_count, u32 words,
                                                                   uint2* __restrict__ table, u32* __restrict__ cv_next, u32* __restrict__ n_classes_next)
+{
+    using BlockReduce = cub::BlockReduce<u32, kBlock>;
+    using BlockScan = cub::BlockScan<u32, kBlock>;
+    __shared__ union { typename BlockReduce::TempStorage reduce; typename BlockScan::TempStorage scan; } temp;
+    __shared__ u32 tile_base;
+    u32 before = 0;
+    for (u32 t = threadIdx.x; t < blockIdx.x; t += kBlock) before += tile_count[t];
+    before = BlockReduce(temp.reduce).Sum(before);
+    if (threadIdx.x == 0) tile_base = before;
+    __syncthreads();
+    static_assert(kWordsPerThread == 4, "one uint4 of bitmap words per thread");
+    const u32 w0 = blockIdx.x * kTileWords + threadIdx.x * kWordsPerThread;
+    const bool full = w0 + kWordsPerThread <= words;
+    u32 bits[kWordsPerThread] = {0, 0, 0, 0};
+    if (full)
+    {
+        const uint4 b = *reinterpret_cast<const uint4*>(bitmap + w0);
+        bits[0] = b.x; bits[1] = b.y; bits[2] = b.z; bits[3] = b.w;
+    }
+    else
+        for (u32 q = 0; q < kWordsPerThread; q++) bits[q] = w0 + q < words ? bitmap[w0 + q] : 0u;
+    const u32 mine = __popc(bits[0]) + __popc(bits[1]) + __popc(bits[2]) + __popc(bits[3]);
+    u32 offset, tile_total;
+    BlockScan(temp.scan).ExclusiveSum(mine, offset, tile_total);
+    u32 r = tile_base + offset;
+    u32 first[kWordsPerThread];
+#pragma unroll
+    for (u32 q = 0; q < kWordsPerThread; q++)
+    {
+        first[q] = r;
+        u32 b = bits[q];
+        while (b)
+        {
+            cv_next[r++] = ((w0 + q) << 5) + (u32) (__ffs(b) - 1);
+            b &= b - 1;
+        }
+    }
+    if (full)
+    {
+        uint4* t = reinterpret_cast<uint4*>(table + w0);
+        t[0] = make_uint4(first[0], bits[0], first[1], bits[1]);
+        t[1] = make_uint4(first[2], bits[2], first[3], bits[3]);
+        if (mine) *reinterpret_cast<uint4*>(bitmap + w0) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    else
+        for (u32 q = 0; q < kWordsPerThread && w0 + q < words; q++)
+        {
+            table[w0 + q] = make_uint2(first[q], bits[q]);
+            bitmap[w0 + q] = 0;
+        }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0)
+    {
+        const u32 total = tile_base + tile_total;
+        table[words] = make_uint2(total, 0u);
+        cv_next[total] = kNoVertex;                    // the class of every walker that stopped
+        *n_classes_next = total + 1;
+    }
+}
+
+// The same from a library scan of the word popcounts (bitmaps of more than kMaxTiles tiles).
+__global__ void __launch_bounds__(kBlock) coalesced_expand_scanned_kernel(u32* __restrict__ bitmap, const u32* __restrict__ word_rank, u32 words,
+                                                                          uint2* __restrict__ table, u32* __restrict__ cv_next, u32* __restrict__ n_classes_next)
 {
     const u32 w = blockIdx.x * kBlock + threadIdx.x;
     if (w == 0)
     {
         const u32 total = word_rank[words];
-        cv_next[total] = kNoVertex;                    // the class of every walker that stopped
+        table[words] = make_uint2(total, 0u);
+        cv_next[total] = kNoVertex;
         *n_classes_next = total + 1;
     }
     if (w >= words) return;
@@ -151,11 +247,11 @@ __global__ void __launch_bounds__(kBlock) coalesced_expand_kernel(u32* __restric
 
 // Last word of every record: final vertex -> its rank among the occupied vertices (dead classes share `total`).
 template <u32 R>
-__global__ void __launch_bounds__(kBlock) coalesced_relabel_kernel(u32* __restrict__ rec, const uint2* __restrict__ table, const u32* __restrict__ word_rank,
-                                                                   u32 words, const u32* __restrict__ n_classes)
+__global__ void __launch_bounds__(kBlock) coalesced_relabel_kernel(u32* __restrict__ rec, const uint2* __restrict__ table, u32 words,
+                                                                   const u32* __restrict__ n_classes)
 {
     const u32 nc = *n_classes;
-    const u32 total = word_rank[words];
+    const u32 total = table[words].x;
     for (u32 c = blockIdx.x * kBlock + threadIdx.x; c < nc; c += gridDim.x * kBlock)
     {
         u32* slot = rec + (u64) c * R + (R - 1);
@@ -217,7 +313,7 @@ struct SegmentCtx
     const LaunchCtx& lc;
     const WalkParams& wp;
     u32 words;
-    unsigned walker_grid, emit_grid, class_grid, word_grid;
+    unsigned walker_grid, emit_grid, class_grid, word_grid, tiles;
     u32 *cls, *rec, *bitmap, *word_rank;
     uint2* table;
     void* scan_temp;
@@ -234,15 +330,25 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
     lc.count();
     if (merge)
     {
-        cub::CountingInputIterator<u32> iota(0);
-        cub::TransformInputIterator<u32, PopcountOf, cub::CountingInputIterator<u32>> pops(iota, PopcountOf{s.bitmap, s.words});
-        size_t bytes = s.scan_temp_bytes;
-        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(s.scan_temp, bytes, pops, s.word_rank, (int) (s.words + 1), lc.stream));
-        lc.count_lib();
-        coalesced_expand_kernel<<<s.word_grid, kBlock, 0, lc.stream>>>(s.bitmap, s.word_rank, s.words, s.table, cv_next, nc_next);
-        coalesced_relabel_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.rec, s.table, s.word_rank, s.words, nc);
+        if (s.tiles <= kMaxTiles)
+        {
+            coalesced_tile_counts_kernel<<<s.tiles, kBlock, 0, lc.stream>>>(s.bitmap, s.words, s.word_rank);
+            coalesced_expand_kernel<<<s.tiles, kBlock, 0, lc.stream>>>(s.bitmap, s.word_rank, s.words, s.table, cv_next, nc_next);
+            lc.count(2);
+        }
+        else
+        {
+            cub::CountingInputIterator<u32> iota(0);
+            cub::TransformInputIterator<u32, PopcountOf, cub::CountingInputIterator<u32>> pops(iota, PopcountOf{s.bitmap, s.words});
+            size_t bytes = s.scan_temp_bytes;
+            WHARF_CUDA(cub::DeviceScan::ExclusiveSum(s.scan_temp, bytes, pops, s.word_rank, (int) (s.words + 1), lc.stream));
+            lc.count_lib();
+            coalesced_expand_scanned_kernel<<<s.word_grid, kBlock, 0, lc.stream>>>(s.bitmap, s.word_rank, s.words, s.table, cv_next, nc_next);
+            lc.count();
+        }
+        coalesced_relabel_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.rec, s.table, s.words, nc);
         coalesced_emit_kernel<R, true><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
-        lc.count(3);
+        lc.count(2);
     }
     else
     {
@@ -253,14 +359,24 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
 }  // namespace
 
 // Scratch of the schedule plus, when no per-replica callback is wanted, the whole pass as one CUDA graph: ~2700
-// kernel launches per generate (scale-25: most of them a few microseconds long) replayed without host work.
-struct CoalescedPlan
+// kernel launches per generate (scale-25: most of them a few microseconds long) replayed without host work.  The
+// replicas are independent, so the graph runs them on up to `branches` parallel branches (each with its own
+// scratch): on a shard of a multi-rank run most kernels are too small to fill the GPU on their own.
+struct CoalescedBranch
 {
     Scratch<u32> cls, cv_a, cv_b, rec, bitmap, word_rank, counts;
     Scratch<uint2> table;
     Scratch<u8> temp;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+};
+
+struct CoalescedPlan
+{
+    std::vector<CoalescedBranch> branch;
     size_t temp_bytes = 0;
     u32 n_local = 0, words = 0;
+    cudaEvent_t fork = nullptr;
     cudaGraphExec_t exec = nullptr;
     u64 graph_launches = 0, graph_lib_calls = 0;
     struct Key
@@ -279,7 +395,16 @@ struct CoalescedPlan
         if (exec) cudaGraphExecDestroy(exec);
         exec = nullptr;
     }
-    ~CoalescedPlan() { drop_graph(); }
+    ~CoalescedPlan()
+    {
+        drop_graph();
+        for (auto& b : branch)
+        {
+            if (b.stream) cudaStreamDestroy(b.stream);
+            if (b.done) cudaEventDestroy(b.done);
+        }
+        if (fork) cudaEventDestroy(fork);
+    }
 };
 
 void coalesced_plan_release(CoalescedPlan*& plan)
@@ -290,60 +415,114 @@ void coalesced_plan_release(CoalescedPlan*& plan)
 
 namespace
 {
-void plan_buffers(CoalescedPlan& pl, const LaunchCtx& lc, u32 nl, u32 words)
+// Parallel branches of the graph: two while one replica's kernels fill the GPU (n_local in the tens of millions; the
+// small class kernels of one replica then overlap the other's emit), more on smaller shards (measured at scale-25:
+// 78.6 -> 73.9 ms on one GPU with 2 branches, 23.8 -> 19.4 ms on a shard of eight with 5+).  WHARF_BRANCHES overrides.
+u32 wanted_branches(u32 nl, u32 wpv)
 {
-    if (pl.n_local == nl && pl.words == words && pl.cls.ptr) return;
-    pl.drop_graph();
-    pl.cls.allocate(lc.stream, nl);
-    pl.cv_a.allocate(lc.stream, (u64) nl + 1);
-    pl.cv_b.allocate(lc.stream, (u64) nl + 1);
-    pl.rec.allocate(lc.stream, ((u64) nl + 1) * kMaxRec);
-    pl.bitmap.allocate(lc.stream, words);
-    pl.word_rank.allocate(lc.stream, (u64) words + 1);
-    pl.counts.allocate(lc.stream, 2);
-    pl.table.allocate(lc.stream, words);
-    cub::CountingInputIterator<u32> iota(0);
-    cub::TransformInputIterator<u32, PopcountOf, cub::CountingInputIterator<u32>> pops(iota, PopcountOf{pl.bitmap.ptr, words});
-    pl.temp_bytes = 0;
-    WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, pl.temp_bytes, pops, pl.word_rank.ptr, (int) (words + 1), lc.stream));
-    pl.temp.allocate(lc.stream, pl.temp_bytes);
-    pl.n_local = nl;
-    pl.words = words;
+    u64 b = std::max<u64>(2, (48ull << 20) / std::max<u32>(nl, 1));
+    if (const char* e = std::getenv("WHARF_BRANCHES")) b = (u64) std::max(1, std::atoi(e));
+    return (u32) std::min<u64>(b, wpv);
 }
 
-void enqueue_pass(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
-                  const std::function<void(u32)>& after_replica)
+void plan_buffers(CoalescedPlan& pl, const LaunchCtx& lc, u32 nl, u32 words, u32 branches)
+{
+    if (pl.n_local == nl && pl.words == words && pl.branch.size() >= branches) return;
+    pl.drop_graph();
+    if (pl.n_local != nl || pl.words != words)
+    {
+        for (auto& b : pl.branch) { if (b.stream) cudaStreamDestroy(b.stream); if (b.done) cudaEventDestroy(b.done); }
+        pl.branch.clear();
+    }
+    pl.n_local = nl;
+    pl.words = words;
+    if (!pl.fork) WHARF_CUDA(cudaEventCreateWithFlags(&pl.fork, cudaEventDisableTiming));
+    while (pl.branch.size() < branches)
+    {
+        pl.branch.emplace_back();
+        CoalescedBranch& b = pl.branch.back();
+        b.cls.allocate(lc.stream, nl);
+        b.cv_a.allocate(lc.stream, (u64) nl + 1);
+        b.cv_b.allocate(lc.stream, (u64) nl + 1);
+        b.rec.allocate(lc.stream, ((u64) nl + 1) * kMaxRec);
+        b.bitmap.allocate(lc.stream, words);
+        b.word_rank.allocate(lc.stream, (u64) words + 1);
+        b.counts.allocate(lc.stream, 2);
+        b.table.allocate(lc.stream, (u64) words + 1);
+        cub::CountingInputIterator<u32> iota(0);
+        cub::TransformInputIterator<u32, PopcountOf, cub::CountingInputIterator<u32>> pops(iota, PopcountOf{b.bitmap.ptr, words});
+        pl.temp_bytes = 0;
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, pl.temp_bytes, pops, b.word_rank.ptr, (int) (words + 1), lc.stream));
+        b.temp.allocate(lc.stream, pl.temp_bytes);
+        if (pl.branch.size() > 1)
+        {
+            WHARF_CUDA(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
+            WHARF_CUDA(cudaEventCreateWithFlags(&b.done, cudaEventDisableTiming));
+        }
+    }
+}
+
+// All segments of replica r on the stream of `lc`, with the scratch of branch `b`.
+void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, const CoalescedPlan& pl,
+                     const CoalescedBranch& b, u32 r)
 {
     const u32 nl = wp.n_local, L = wp.L, words = pl.words;
-    WHARF_CUDA(cudaMemsetAsync(pl.bitmap.ptr, 0, (u64) words * 4, lc.stream));
-    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), div_up(nl, kBlock * kEmitWalkers), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock), pl.cls.ptr, pl.rec.ptr, pl.bitmap.ptr,
-                 pl.word_rank.ptr, pl.table.ptr, pl.temp.ptr, pl.temp_bytes, d_steps};
+    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), div_up(nl, kBlock * kEmitWalkers), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock),
+                 div_up(words, kTileWords), b.cls.ptr, b.rec.ptr, b.bitmap.ptr, b.word_rank.ptr, b.table.ptr, b.temp.ptr, pl.temp_bytes, d_steps};
+    u32 *cv = b.cv_a.ptr, *cv_next = b.cv_b.ptr, *nc = b.counts.ptr, *nc_next = b.counts.ptr + 1;
+    u32* col = wp.walks + (u64) r * nl;                       // column block of the replica in every corpus row
+    coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(b.cls.ptr, cv, col, nl, wp.rank, wp.world, nc);
+    lc.count();
+    for (u32 a = 0; a < L;)
+    {
+        const u32 R = record_words(a);
+        const u32 k = std::min(R - 1, L - a);                 // draws a .. a + k - 1
+        SegDraws draws{};
+        for (u32 j = 0; j < k; j++) draws.x[j] = host_draw[(u64) r * L + a + j];
+        const u32 stored = std::min(k, L - 1 - a);            // cells a + 1 .. a + stored exist; the last draw is only counted
+        const bool merge = a + k < L;
+        u32* first_row = col + (u64) (a + 1) * wp.w_local;
+        switch (R)
+        {
+            case 2: run_segment<2>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+            case 4: run_segment<4>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+            default: run_segment<8>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+        }
+        if (merge) { std::swap(cv, cv_next); std::swap(nc, nc_next); }
+        a += k;
+    }
+    WHARF_CUDA(cudaGetLastError());
+}
+
+// One replica after the other on the caller's stream.
+void enqueue_serial(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
+                    const std::function<void(u32)>& after_replica)
+{
+    const CoalescedBranch& b = pl.branch[0];
+    WHARF_CUDA(cudaMemsetAsync(b.bitmap.ptr, 0, (u64) pl.words * 4, lc.stream));
     for (u32 r = 0; r < wp.wpv; r++)
     {
-        u32 *cv = pl.cv_a.ptr, *cv_next = pl.cv_b.ptr, *nc = pl.counts.ptr, *nc_next = pl.counts.ptr + 1;
-        u32* col = wp.walks + (u64) r * nl;                       // column block of the replica in every corpus row
-        coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(pl.cls.ptr, cv, col, nl, wp.rank, wp.world, nc);
-        lc.count();
-        for (u32 a = 0; a < L;)
-        {
-            const u32 R = record_words(a);
-            const u32 k = std::min(R - 1, L - a);                 // draws a .. a + k - 1
-            SegDraws draws{};
-            for (u32 j = 0; j < k; j++) draws.x[j] = host_draw[(u64) r * L + a + j];
-            const u32 stored = std::min(k, L - 1 - a);            // cells a + 1 .. a + stored exist; the last draw is only counted
-            const bool merge = a + k < L;
-            u32* first_row = col + (u64) (a + 1) * wp.w_local;
-            switch (R)
-            {
-                case 2: run_segment<2>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
-                case 4: run_segment<4>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
-                default: run_segment<8>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
-            }
-            if (merge) { std::swap(cv, cv_next); std::swap(nc, nc_next); }
-            a += k;
-        }
-        WHARF_CUDA(cudaGetLastError());
+        enqueue_replica(lc, wp, host_draw, d_steps, pl, b, r);
         if (after_replica) after_replica(r);
+    }
+}
+
+// Inside a stream capture: replica r on branch r % branches; the extra branches fork from and join the caller's stream.
+void enqueue_forked(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl, u32 branches)
+{
+    WHARF_CUDA(cudaEventRecord(pl.fork, lc.stream));
+    for (u32 i = 0; i < branches; i++)
+    {
+        const CoalescedBranch& b = pl.branch[i];
+        LaunchCtx blc = lc;
+        if (i) { blc.stream = b.stream; WHARF_CUDA(cudaStreamWaitEvent(b.stream, pl.fork, 0)); }
+        WHARF_CUDA(cudaMemsetAsync(b.bitmap.ptr, 0, (u64) pl.words * 4, blc.stream));
+        for (u32 r = i; r < wp.wpv; r += branches) enqueue_replica(blc, wp, host_draw, d_steps, pl, b, r);
+    }
+    for (u32 i = 1; i < branches; i++)
+    {
+        WHARF_CUDA(cudaEventRecord(pl.branch[i].done, pl.branch[i].stream));
+        WHARF_CUDA(cudaStreamWaitEvent(lc.stream, pl.branch[i].done, 0));
     }
 }
 
@@ -366,10 +545,12 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
         if (!*plan_slot) *plan_slot = new CoalescedPlan();
         pl = *plan_slot;
     }
-    plan_buffers(*pl, lc, wp.n_local, words);
-    if (after_replica || !plan_slot || !graphs_enabled())
+    const bool as_graph = !after_replica && plan_slot && graphs_enabled();
+    const u32 branches = as_graph ? wanted_branches(wp.n_local, wp.wpv) : 1;
+    plan_buffers(*pl, lc, wp.n_local, words, branches);
+    if (!as_graph)
     {
-        enqueue_pass(lc, wp, host_draw, d_steps, *pl, after_replica);
+        enqueue_serial(lc, wp, host_draw, d_steps, *pl, after_replica);
         return;
     }
     u64 draw_hash = 1469598103934665603ull;
@@ -386,7 +567,7 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
         WHARF_CUDA(cudaStreamBeginCapture(lc.stream, cudaStreamCaptureModeThreadLocal));
         try
         {
-            enqueue_pass(cap, wp, host_draw, d_steps, *pl, nullptr);
+            enqueue_forked(cap, wp, host_draw, d_steps, *pl, branches);
         }
         catch (...)
         {

@@ -538,14 +538,14 @@ i64 global_to_local(const wmh_engine& e, u64 walk_id)
     const u64 n = e.g.n;
     if (!e.have_walks || walk_id >= n * e.walks_wpv) return -1;
     const u64 replica = walk_id / n, start = walk_id % n;
-    if (start % e.cfg.world != e.cfg.rank) return -1;
+    if (shard_owner((u32) start, e.cfg.world, n) != e.cfg.rank) return -1;
     return (i64) (replica * e.n_local + start / e.cfg.world);
 }
 
 u64 local_to_global(const wmh_engine& e, u64 local)
 {
     const u64 replica = local / e.n_local, s = local % e.n_local;
-    return replica * e.g.n + s * e.cfg.world + e.cfg.rank;
+    return replica * e.g.n + shard_start((u32) s, e.cfg.rank, e.cfg.world, e.g.n);
 }
 
 void fetch_walk(wmh_engine& e, u64 local, std::vector<u32>& row)
@@ -960,6 +960,21 @@ uint64_t wmh_local_to_global_walk(const wmh_engine* e, uint64_t local_walk)
 }
 
 int64_t wmh_global_to_local_walk(const wmh_engine* e, uint64_t walk_id) { return e ? global_to_local(*e, walk_id) : -1; }
+
+uint32_t wmh_walk_owner(const wmh_engine* e, uint64_t walk_id)
+{
+    if (!e || e->g.n == 0) return 0;
+    return shard_owner((u32) (walk_id % e->g.n), e->cfg.world, e->g.n);
+}
+
+uint64_t wmh_local_start_vertices(const wmh_engine* e, uint32_t* out, uint64_t capacity)
+{
+    if (!e) return 0;
+    const u32 nl = local_starts(e->g.n, e->cfg.rank, e->cfg.world);
+    if (out)
+        for (u32 i = 0; i < nl && i < capacity; i++) out[i] = shard_start(i, e->cfg.rank, e->cfg.world, e->g.n);
+    return nl;
+}
 
 int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum)
 {

@@ -81,12 +81,12 @@ __device__ __forceinline__ void store_record(u32* __restrict__ rec, u32 c, const
 
 // cls[i] = i, vertex of class i = start vertex of local walker i, first corpus row of the replica.
 __global__ void __launch_bounds__(kBlock) coalesced_init_kernel(u32* __restrict__ cls, u32* __restrict__ cv, u32* __restrict__ row0, u32 n_local,
-                                                                u32 rank, u32 world, u32* __restrict__ n_classes)
+                                                                u32 rank, u32 world, u64 n, u32* __restrict__ n_classes)
 {
     const u32 i = blockIdx.x * kBlock + threadIdx.x;
     if (i == 0) *n_classes = n_local;
     if (i >= n_local) return;
-    const u32 v = i * world + rank;                  // = walk_id % n (wharfmh.h:292)
+    const u32 v = shard_start(i, rank, world, n);    // = walk_id % n (wharfmh.h:292)
     cls[i] = i;
     cv[i] = v;
     row0[i] = v;
@@ -471,7 +471,7 @@ void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_
                  div_up(words, kTileWords), b.cls.ptr, b.rec.ptr, b.bitmap.ptr, b.word_rank.ptr, b.table.ptr, b.temp.ptr, pl.temp_bytes, d_steps};
     u32 *cv = b.cv_a.ptr, *cv_next = b.cv_b.ptr, *nc = b.counts.ptr, *nc_next = b.counts.ptr + 1;
     u32* col = wp.walks + (u64) r * nl;                       // column block of the replica in every corpus row
-    coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(b.cls.ptr, cv, col, nl, wp.rank, wp.world, nc);
+    coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(b.cls.ptr, cv, col, nl, wp.rank, wp.world, wp.n, nc);
     lc.count();
     for (u32 a = 0; a < L;)
     {

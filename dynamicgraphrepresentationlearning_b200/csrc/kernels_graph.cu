@@ -500,7 +500,11 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity)
     lc.count();
     exclusive_sum(lc, deg.ptr, begin.ptr, g.n + 1);
     tr.mark("compact: degrees+scan");
-    if (g.spare.count < capacity) g.spare.allocate(capacity);
+    // the spare pool (the previous pool, or the one sized by graph_enable_tails) is reused as long as it leaves an eighth
+    // of slack: growing it means a fresh device allocation of the whole pool (measured: 0.9 s inside an edge batch on
+    // the LiveJournal-shape graph), and m only drifts by a fraction of a percent per batch
+    const u64 need = live + extra_capacity;
+    if (g.spare.count < need + need / 8) g.spare.allocate(capacity);
     tr.mark("compact: spare pool");
     copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, begin.ptr, g.spare.ptr);
     tr.mark("compact: copy_all_rows");

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(256) encode_codes_kernel(const u32* __restrict
     const u32 pos = (u32) (cell / w_local);
     const u64 w = cell - (u64) pos * w_local;
     const u32 replica = (u32) (w / n_local);
-    const u64 walk_id = (u64) replica * n + (u64) (w - (u64) replica * n_local) * world + rank;
+    const u64 walk_id = (u64) replica * n + shard_start((u32) (w - (u64) replica * n_local), rank, world, n);
     u32 next = kRefSentinel;
     if (pos + 1 < L)
     {

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkP
         const u32 replica = (u32) (w / p.n_local);                  // = walk_id / n  (wharfmh.h:291)
         if (!kRewalk)
         {
-            cur = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;   // = walk_id % n (wharfmh.h:292)
+            cur = shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n);   // = walk_id % n (wharfmh.h:292)
             p.walks[w] = cur;
         }
         const u64* __restrict__ X = p.draw + (u64) replica * p.L;   // stream restarts at the re-walk point (:814-816)
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkP
         alive[k] = w < p.w_local;
         const u32 replica = alive[k] ? (u32) (w / p.n_local) : 0;
         rep_off[k] = replica * p.L;
-        cur[k] = alive[k] ? (u32) (w - (u64) replica * p.n_local) * p.world + p.rank : 0;
+        cur[k] = alive[k] ? shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n) : 0;
         if (alive[k]) p.walks[w] = cur[k];
     }
     bool live[kWalks];          // walker still moving (alive and not stopped on a degree-0 vertex)
@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
     {
         if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = p.first + t; }
         const u32 replica = (u32) (w / p.n_local);
-        const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
+        const u32 start = shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n);
         walk_id = (u64) replica * p.n + start;                       // global id keys the draws
         if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
         else { cur = start; p.walks[w] = cur; }
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkPar
         u32 pos = 0, cur;
         if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = p.first + t; }
         const u32 replica = (u32) (w / p.n_local);
-        const u32 start = (u32) (w - (u64) replica * p.n_local) * p.world + p.rank;
+        const u32 start = shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n);
         const u64 walk_id = (u64) replica * p.n + start;
         if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
         else { cur = start; p.walks[w] = cur; }

@@ -2,7 +2,8 @@
 two exchanges the path has.
 
 The reference is single-process; this is the B200 scale-out of the same API.  Walks shard by
-start vertex (start % world == rank), every rank holds a full replica of the graph, and no collective runs
+start vertex (one vertex of every block of `world` consecutive ids per rank, rotated from block to block:
+wmh_walk_owner / wmh_local_start_vertices), every rank holds a full replica of the graph, and no collective runs
 while walking.  Per edge batch:
   C1  broadcast of the batch from the source rank (<= 16 MB for 2 M edges), so every replica merges the
       same edges;
@@ -132,7 +133,7 @@ class ShardedWharfMH:
 
     def walk(self, walk_id: int) -> str:
         """graph/wharfmh.h:365 for any global walk id: the owner broadcasts the text."""
-        owner = (walk_id % self.number_of_vertices()) % self.world
+        owner = self.engine.walk_owner(walk_id)
         box = [self.engine.walk(walk_id) if self.rank == owner else None]
         dist.broadcast_object_list(box, src=owner, group=self.group)
         return box[0]

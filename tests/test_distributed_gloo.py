@@ -46,6 +46,9 @@ class OracleShard:
     def delete_edges_batch(self, edges, sorted=False, remove_dups=False, apply_walk_updates=True):
         return self._update(edges, True, remove_dups, apply_walk_updates)
 
+    def walk_owner(self, walk_id):
+        return int((walk_id % self.n) % self.cfg.world)
+
     def local_walk_ids(self):
         starts = np.arange(self.cfg.rank, self.n, self.cfg.world, dtype=np.uint64)
         return (np.arange(self.cfg.walks_per_vertex, dtype=np.uint64)[:, None] * np.uint64(self.n) + starts[None, :]).reshape(-1)

@@ -237,7 +237,7 @@ def test_inverted_index_find_next(wharf, wo):
 
 
 def test_sharded_corpus_equals_global(wharf, wo):
-    """Walks shard by start vertex (start % world == rank) with the graph replicated; the union of the shards
+    """Walks shard by start vertex (wmh_walk_owner) with the graph replicated; the union of the shards
     must be the single-engine corpus, before and after batches."""
     n = 1 << 9
     off, adj = wo.rmat_graph(9, 3000)
@@ -265,6 +265,33 @@ def test_sharded_corpus_equals_global(wharf, wo):
             e.destroy()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,world", [(512, 2), (509, 3), (1000, 8), (7, 8), (64, 5)])
+def test_shard_rule_is_a_partition(wharf, n, world):
+    """Every vertex is the start vertex of exactly one rank, ascending per rank, consistent with wmh_walk_owner and
+    with the local <-> global walk id maps; rank r owns ceil((n - r) / world) starts."""
+    off = np.zeros(n, dtype=np.uint64)
+    adj = np.zeros(0, dtype=np.uint32)
+    seen = np.full(n, -1, dtype=np.int64)
+    for r in range(world):
+        with make(wharf, n, off, adj, walks_per_vertex=2, walk_length=3, rank=r, world=world) as e:
+            starts = e.local_start_vertices().astype(np.int64)
+            assert starts.shape[0] == (n - r + world - 1) // world if r < n else starts.shape[0] == 0
+            assert (np.diff(starts) > 0).all()
+            assert (seen[starts] == -1).all()
+            seen[starts] = r
+            assert all(e.walk_owner(int(v)) == r and e.walk_owner(int(n + v)) == r for v in starts[:50])
+            e.generate_initial_random_walks()
+            ids = e.local_walk_ids()
+            assert np.array_equal(ids[: starts.shape[0]], starts.astype(np.uint64))
+            assert all(e.global_to_local_walk(int(g)) == i for i, g in enumerate(ids[:40]))
+            assert np.array_equal(e.walks()[:, 0], (ids % np.uint64(n)).astype(np.uint32))
+    assert (seen >= 0).all()
+    if world == 8 and n == 1000:
+        assert len({int(seen[b * 8]) for b in range(100)}) > 1          # rotated from block to block
+
+
+@pytest.mark.gpu
 def test_pairings_device(wharf, golden):
     import ctypes as C
     import torch

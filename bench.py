@@ -304,7 +304,7 @@ def main():
         bytes_per_step = mh_bytes_per_step(torch, d_offsets, sample) if spec["model"] == "node2vec" else BYTES_PER_DET_STEP
     if spec["det"]:
         coalesced = n * 8 + m * 4 > (96 << 20)          # engine's GENERATE_AUTO rule (engine.cu use_coalesced)
-        kernel_name = ("coalesced_{advance,rank,emit}_kernel segments (kernels_coalesced.cu), one generate pass" if coalesced
+        kernel_name = ("coalesced_{advance,tile_counts,expand,relabel,emit}_kernel segments (kernels_coalesced.cu), one generate pass replayed as a CUDA graph" if coalesced
                        else "walk_deterministic_ilp_kernel<1,256,0>")
     else:
         kernel_name = "walk_n2v_kernel<false>" if spec["model"] == "node2vec" else "walk_deepwalk_mh_kernel<false>"

@@ -62,8 +62,11 @@ __device__ __forceinline__ void load_record(const u32* __restrict__ rec, u32 c, 
     else if constexpr (R == 4) { const uint4 a = __ldg(reinterpret_cast<const uint4*>(rec) + c); t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; }
     else
     {
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(rec) + 2 * (u64) c), b = __ldg(reinterpret_cast<const uint4*>(rec) + 2 * (u64) c + 1);
-        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
+        // one 256-bit load (sm_100: LDG.E.ENL2.256): the whole sector in one request - the scattered record gather is
+        // bound by L1 wavefronts (one per distinct sector and instruction), and two 128-bit loads would cost two
+        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(t[0]), "=r"(t[1]), "=r"(t[2]), "=r"(t[3]), "=r"(t[4]), "=r"(t[5]), "=r"(t[6]), "=r"(t[7])
+                     : "l"(rec + 8 * (u64) c));
     }
 }
 

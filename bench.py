@@ -291,6 +291,15 @@ def main():
     value = total_steps / device_s
     kernel_avg_ms = sum(kernel_ms) / len(kernel_ms)
 
+    # ---- the inverted index over the corpus (walks/inverted_index.h): derived on demand by one device radix sort; the
+    # timed step above stores the corpus as the walk matrix and finds affected walks by scanning it (search_mode SCAN) ----
+    index_build_ms = None
+    if (n * WPV // world) * LEN < (1 << 32):
+        torch.cuda.synchronize()
+        t_idx = time.perf_counter()
+        engine.build_index()
+        index_build_ms = max_over_ranks(1e3 * (time.perf_counter() - t_idx))
+
     # ---- roofline of the dominant kernel (walk kernel), rank 0's launch ----
     peaks = {}
     peaks_path = ROOT / "MEASURED_PEAKS.json"
@@ -451,6 +460,7 @@ def main():
                        "l2": "explicit 256 MiB write between timed steps"},
             "clocks": clocks.summary(), "gpu_launches": launches, "wall_s_timed_region": wall,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "updates": updates,
+            "index_build_ms": index_build_ms,
         }
         line.update(extra)
         print(json.dumps(line), flush=True)

@@ -375,13 +375,15 @@ void generate(wmh_engine& e, u32* host_out = nullptr)
     bool exchanged = false;
     if (needs_memo(e))
     {
-        graph_aux_clear_caches(lc, e.g);                 // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90)
+        // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90): every cache is emptied, or - with
+        // peers - overwritten by the value its first touch would compute (every state belongs to one rank's share)
         if (peer_usable(e))
         {
             n2v_share_sampler_init(lc, walk_params(e), e.g.m, e.peer);
             exchanged = true;
         }
-        else if (e.cfg.world == 1 && std::getenv("WHARF_EAGER_INIT") && std::atoi(std::getenv("WHARF_EAGER_INIT")))
+        else graph_aux_clear_caches(lc, e.g);
+        if (!exchanged && e.cfg.world == 1 && std::getenv("WHARF_EAGER_INIT") && std::atoi(std::getenv("WHARF_EAGER_INIT")))
         {
             // tuning aid: the same bulk kernel on one rank (every state initialised up front instead of at first touch)
             Scratch<u8> flags(e.stream, kPeerFlagBytes);

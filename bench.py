@@ -295,6 +295,7 @@ def main():
     # timed step above stores the corpus as the walk matrix and finds affected walks by scanning it (search_mode SCAN) ----
     index_build_ms = None
     if (n * WPV // world) * LEN < (1 << 32):
+        engine.build_index()                                             # first build grows the device memory pool
         torch.cuda.synchronize()
         t_idx = time.perf_counter()
         engine.build_index()

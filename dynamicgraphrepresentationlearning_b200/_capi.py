@@ -92,7 +92,7 @@ SIGNATURES = {
     "wmh_local_to_global_walk": (u64, [vp, u64]),
     "wmh_global_to_local_walk": (C.c_int64, [vp, u64]),
     "wmh_walk_owner": (u32, [vp, u64]),
-    "wmh_local_start_vertices": (u64, [vp, vp, u64]),
+    "wmh_local_walk_ids": (u64, [vp, vp, u64]),
     "wmh_corpus_fingerprint": (i32, [vp, PU64]),
     "wmh_build_index": (i32, [vp]),
     "wmh_index_find_next": (i32, [vp, u32, u64, u32, PU32, C.POINTER(i32)]),

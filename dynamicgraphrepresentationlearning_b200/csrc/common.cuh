@@ -171,6 +171,81 @@ __host__ __device__ __forceinline__ u32 shard_owner(u32 vertex, u32 world, u64 n
     return block < (u32) (n / world) ? (slot + world - shard_rotation(block, world)) % world : slot;
 }
 
+// Which walks a rank owns.  Replicas (walk_id / n) are independent, so whole replicas go first: with q = wpv / world
+// every rank owns the q replicas [rank * q, rank * q + q) entirely (all n start vertices); the remaining wpv - world * q
+// replicas are sharded by start vertex (shard_start above).  Whole replicas keep the deterministic coalesced schedule
+// at its single-GPU efficiency (the walkers of a replica merge as on one GPU); wpv < world degenerates to pure start-
+// vertex sharding, wpv % world == 0 to pure replica sharding.  Local walk order: the whole replicas (start ascending),
+// then the sharded ones (owned starts ascending), i.e. ascending global walk id.
+struct ShardMap
+{
+    u64 n = 0;                // vertices
+    u32 rank = 0, world = 1;
+    u32 whole = 0;            // replicas owned entirely
+    u32 whole_first = 0;      // first of them (global replica number)
+    u32 shared = 0;           // replicas sharded by start vertex
+    u32 shared_first = 0;     // first of them
+    u32 n_local = 0;          // start vertices this rank owns in a sharded replica
+
+    __host__ __device__ u64 whole_walks() const { return (u64) whole * n; }
+    __host__ __device__ u64 local_walks() const { return whole_walks() + (u64) shared * n_local; }
+    // local walk -> (global replica, start vertex)
+    __host__ __device__ void locate(u64 w, u32& replica, u32& start) const
+    {
+        const u64 ww = whole_walks();
+        if (w < ww)
+        {
+            const u32 r = (u32) (w / n);
+            replica = whole_first + r;
+            start = (u32) (w - (u64) r * n);
+        }
+        else
+        {
+            const u64 x = w - ww;
+            const u32 r = (u32) (x / n_local);
+            replica = shared_first + r;
+            start = shard_start((u32) (x - (u64) r * n_local), rank, world, n);
+        }
+    }
+    __host__ __device__ u64 global_id(u64 w) const
+    {
+        u32 replica, start;
+        locate(w, replica, start);
+        return (u64) replica * n + start;
+    }
+    // rank that owns a global walk id
+    __host__ __device__ u32 owner(u64 walk_id) const
+    {
+        const u32 replica = (u32) (walk_id / n);
+        if (replica < shared_first) return whole ? replica / whole : 0u;      // every rank owns the same number of whole replicas
+        return shard_owner((u32) (walk_id % n), world, n);
+    }
+    // local index of an owned global walk id, -1 otherwise
+    __host__ __device__ i64 local_of(u64 walk_id) const
+    {
+        if (owner(walk_id) != rank) return -1;
+        const u32 replica = (u32) (walk_id / n);
+        const u32 start = (u32) (walk_id % n);
+        if (replica < shared_first) return (i64) ((u64) (replica - whole_first) * n + start);
+        return (i64) (whole_walks() + (u64) (replica - shared_first) * n_local + start / world);
+    }
+};
+
+inline ShardMap make_shard_map(u64 n, u32 wpv, u32 rank, u32 world)
+{
+    ShardMap m;
+    m.n = n;
+    m.rank = rank;
+    m.world = world;
+    const u32 q = world > 1 ? wpv / world : 0;       // one rank: everything is "sharded" over a world of one
+    m.whole = q;
+    m.whole_first = rank * q;
+    m.shared_first = world > 1 ? world * q : 0;
+    m.shared = wpv - m.shared_first;
+    m.n_local = rank < n ? (u32) ((n - rank + world - 1) / world) : 0;
+    return m;
+}
+
 __device__ __forceinline__ u32 filter_hash(u32 x)
 {
     x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;

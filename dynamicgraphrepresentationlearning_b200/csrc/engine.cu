@@ -82,7 +82,7 @@ struct wmh_engine
     DeviceBuffer<u32> walks;           // [L][w_local]
     bool have_walks = false;
     u64 w_local = 0;
-    u32 n_local = 0;
+    ShardMap map;                      // which walks this rank owns (fixed when the corpus is generated)
     u32 walks_L = 0, walks_wpv = 0;
 
     DeviceIndex index;
@@ -209,9 +209,10 @@ void finish_graph(wmh_engine& e, u64 n, u64 m, const u64* d_offsets, const u32* 
     tr.mark("create: graph buffers+copy");
 }
 
-u32 local_starts(u64 n, u32 rank, u32 world) { return rank < n ? (u32) ((n - rank + world - 1) / world) : 0; }
+// The partition of the walks the engine would use for a corpus generated now.
+ShardMap config_map(const wmh_engine& e) { return make_shard_map(e.g.n, e.cfg.walks_per_vertex, e.cfg.rank, e.cfg.world); }
 
-u64 local_walk_capacity(const wmh_engine* e) { return (u64) local_starts(e->g.n, e->cfg.rank, e->cfg.world) * e->cfg.walks_per_vertex; }
+u64 local_walk_capacity(const wmh_engine* e) { return config_map(*e).local_walks(); }
 
 WalkParams walk_params(wmh_engine& e)
 {
@@ -224,11 +225,9 @@ WalkParams walk_params(wmh_engine& e)
     wp.walks = e.walks.ptr;
     wp.n = e.g.n;
     wp.w_local = e.w_local;
-    wp.n_local = e.n_local;
+    wp.map = e.map;
     wp.wpv = e.walks_wpv;
     wp.L = e.walks_L;
-    wp.rank = e.cfg.rank;
-    wp.world = e.cfg.world;
     wp.model = e.cfg.model;
     wp.deterministic = e.cfg.deterministic;
     wp.init_strategy = e.cfg.init_strategy;
@@ -320,8 +319,7 @@ void generate_and_export(wmh_engine& e, u32* host_out)
     const WalkParams wp = walk_params(e);
     if (use_coalesced(e))
     {
-        const u64 nl = e.n_local;
-        walks_generate_coalesced(lc, wp, e.host_draw.data(), e.d_steps.ptr, [&](u32 replica) { export_range((u64) replica * nl, nl); }, &e.coalesced_plan);
+        walks_generate_coalesced(lc, wp, e.host_draw.data(), e.d_steps.ptr, [&](u64 first, u64 count) { export_range(first, count); }, &e.coalesced_plan);
     }
     else
     {
@@ -345,8 +343,8 @@ void generate(wmh_engine& e, u32* host_out = nullptr)
     validate_config(e.cfg);
     auto lc = e.lc();
     const u32 wpv = e.cfg.walks_per_vertex, L = e.cfg.walk_length;
-    e.n_local = local_starts(e.g.n, e.cfg.rank, e.cfg.world);
-    e.w_local = (u64) e.n_local * wpv;
+    e.map = config_map(e);
+    e.w_local = e.map.local_walks();
     if (e.w_local >= (1ull << 32)) throw std::invalid_argument("more than 2^32 walks per rank are not supported");
     e.walks_L = L;
     e.walks_wpv = wpv;
@@ -537,18 +535,11 @@ int update_device(wmh_engine* e, u64 m, const u32* d_edges, int remove_dups, int
 
 i64 global_to_local(const wmh_engine& e, u64 walk_id)
 {
-    const u64 n = e.g.n;
-    if (!e.have_walks || walk_id >= n * e.walks_wpv) return -1;
-    const u64 replica = walk_id / n, start = walk_id % n;
-    if (shard_owner((u32) start, e.cfg.world, n) != e.cfg.rank) return -1;
-    return (i64) (replica * e.n_local + start / e.cfg.world);
+    if (!e.have_walks || walk_id >= e.g.n * e.walks_wpv) return -1;
+    return e.map.local_of(walk_id);
 }
 
-u64 local_to_global(const wmh_engine& e, u64 local)
-{
-    const u64 replica = local / e.n_local, s = local % e.n_local;
-    return replica * e.g.n + shard_start((u32) s, e.cfg.rank, e.cfg.world, e.g.n);
-}
+u64 local_to_global(const wmh_engine& e, u64 local) { return e.map.global_id(local); }
 
 void fetch_walk(wmh_engine& e, u64 local, std::vector<u32>& row)
 {
@@ -581,7 +572,7 @@ void ensure_codes(wmh_engine& e)
     if (e.g.n * e.walks_wpv * (u64) e.walks_L >= (1ull << 32)) throw std::domain_error("paired corpus needs walks * walk_length < 2^32 (u64 Szudzik domain)");
     auto lc = e.lc();
     e.codes.ensure(std::max<u64>(1, e.index.entries));
-    compressed_walks_encode(lc, e.index, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.n_local, e.cfg.rank, e.cfg.world, e.codes.ptr);
+    compressed_walks_encode(lc, e.index, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.map, e.codes.ptr);
     WHARF_CUDA(cudaStreamSynchronize(e.stream));
     e.codes_valid = true;
 }
@@ -807,7 +798,7 @@ uint64_t wmh_number_of_walks(const wmh_engine* e) { return e ? e->g.n * (e->have
 uint64_t wmh_number_of_local_walks(const wmh_engine* e)
 {
     if (!e) return 0;
-    return e->have_walks ? e->w_local : (u64) local_starts(e->g.n, e->cfg.rank, e->cfg.world) * e->cfg.walks_per_vertex;
+    return e->have_walks ? e->w_local : local_walk_capacity(e);
 }
 
 int wmh_insert_edges_batch(wmh_engine* e, uint64_t m, uint32_t* edges, int sorted, int remove_dups, uint64_t, int apply, uint64_t* n_affected)
@@ -966,16 +957,17 @@ int64_t wmh_global_to_local_walk(const wmh_engine* e, uint64_t walk_id) { return
 uint32_t wmh_walk_owner(const wmh_engine* e, uint64_t walk_id)
 {
     if (!e || e->g.n == 0) return 0;
-    return shard_owner((u32) (walk_id % e->g.n), e->cfg.world, e->g.n);
+    return (e->have_walks ? e->map : config_map(*e)).owner(walk_id);
 }
 
-uint64_t wmh_local_start_vertices(const wmh_engine* e, uint32_t* out, uint64_t capacity)
+uint64_t wmh_local_walk_ids(const wmh_engine* e, uint64_t* out, uint64_t capacity)
 {
     if (!e) return 0;
-    const u32 nl = local_starts(e->g.n, e->cfg.rank, e->cfg.world);
+    const ShardMap m = e->have_walks ? e->map : config_map(*e);
+    const u64 count = m.local_walks();
     if (out)
-        for (u32 i = 0; i < nl && i < capacity; i++) out[i] = shard_start(i, e->cfg.rank, e->cfg.world, e->g.n);
-    return nl;
+        for (u64 w = 0; w < count && w < capacity; w++) out[w] = m.global_id(w);
+    return count;
 }
 
 int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum)

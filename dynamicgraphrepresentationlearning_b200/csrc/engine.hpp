@@ -160,9 +160,8 @@ struct WalkParams
     u32* walks = nullptr;            // [L][W_local] position-major
     u64 n = 0;                       // global vertices
     u64 w_local = 0;                 // local walks
-    u32 n_local = 0;                 // local start vertices
+    ShardMap map;                    // which walks this rank owns, local walk -> (replica, start vertex)
     u32 wpv = 0, L = 0;
-    u32 rank = 0, world = 1;
     u32 model = 0, deterministic = 1, init_strategy = 2;
     float p = 1.f, q = 1.f;
     u64 seed = 0;
@@ -176,12 +175,12 @@ void walks_rewalk(const LaunchCtx& lc, const WalkParams& wp, const u32* d_affect
                   unsigned long long* d_steps);
 // Deterministic mode only: step-synchronous generation that advances walkers standing on the same vertex once
 // (kernels_coalesced.cu).  host_draw = X[wpv][L] on the host.
-// after_replica(r), when given, is called once replica r's column block [r * n_local, (r + 1) * n_local) has been
-// fully enqueued on lc.stream.
+// after_replica(first, count), when given, is called once the local walks [first, first + count) of one replica have
+// been fully enqueued on lc.stream.
 struct CoalescedPlan;                       // scratch + captured CUDA graph of one generate pass (kernels_coalesced.cu)
 void coalesced_plan_release(CoalescedPlan*& plan);
 void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
-                              const std::function<void(u32)>& after_replica, CoalescedPlan** plan_slot);
+                              const std::function<void(u64, u64)>& after_replica, CoalescedPlan** plan_slot);
 // Bulk generation of the local walks [first, first + count) with one walker per thread.
 void walks_generate_range(const LaunchCtx& lc, const WalkParams& wp, u64 first, u64 count, unsigned long long* d_steps);
 // min_pos[w] = first position whose vertex is in the touched bitmap (kNoPos when none).
@@ -208,7 +207,7 @@ u64  index_count_touched(const LaunchCtx& lc, const DeviceIndex& idx, const u32*
 void index_find_next(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u32 vertex,
                      u64 local_walk, u32 position, u32* d_out2 /* [next, found] */);
 void compressed_walks_encode(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u64 n,
-                             u32 n_local, u32 rank, u32 world, u64* d_codes);
+                             const ShardMap& map, u64* d_codes);
 void compressed_find_next(const LaunchCtx& lc, const u64* d_codes, u64 count, u64 walk_id, u32 position, u32 L, u32* d_out2);
 
 // ---- pairing kernels (kernels_pairings.cu) --------------------------------------------------------

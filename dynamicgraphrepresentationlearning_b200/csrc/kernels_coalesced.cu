@@ -316,6 +316,7 @@ struct SegmentCtx
     const LaunchCtx& lc;
     const WalkParams& wp;
     u32 words;
+    u32 nl;                          // walkers of the replica on this rank
     unsigned walker_grid, emit_grid, class_grid, word_grid, tiles;
     u32 *cls, *rec, *bitmap, *word_rank;
     uint2* table;
@@ -350,12 +351,12 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
             lc.count();
         }
         coalesced_relabel_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.rec, s.table, s.words, nc);
-        coalesced_emit_kernel<R, true><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
+        coalesced_emit_kernel<R, true><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.nl, s.d_steps);
         lc.count(2);
     }
     else
     {
-        coalesced_emit_kernel<R, false><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.wp.n_local, s.d_steps);
+        coalesced_emit_kernel<R, false><<<s.emit_grid, kBlock, 0, lc.stream>>>(s.cls, s.rec, first_row, s.wp.w_local, stored, s.nl, s.d_steps);
         lc.count();
     }
 }
@@ -386,11 +387,12 @@ struct CoalescedPlan
     {
         const void *desc, *pool, *walks, *steps;
         u64 n, w_local, draw_hash;
-        u32 n_local, wpv, L, rank, world;
+        u32 n_local, wpv, L, rank, world, whole;
         bool operator==(const Key& o) const
         {
             return desc == o.desc && pool == o.pool && walks == o.walks && steps == o.steps && n == o.n && w_local == o.w_local &&
-                   draw_hash == o.draw_hash && n_local == o.n_local && wpv == o.wpv && L == o.L && rank == o.rank && world == o.world;
+                   draw_hash == o.draw_hash && n_local == o.n_local && wpv == o.wpv && L == o.L && rank == o.rank && world == o.world &&
+                   whole == o.whole;
         }
     } key{};
     void drop_graph()
@@ -421,11 +423,11 @@ namespace
 // Parallel branches of the graph: two while one replica's kernels fill the GPU (n_local in the tens of millions; the
 // small class kernels of one replica then overlap the other's emit), more on smaller shards (measured at scale-25:
 // 78.6 -> 73.9 ms on one GPU with 2 branches, 23.8 -> 19.4 ms on a shard of eight with 5+).  WHARF_BRANCHES overrides.
-u32 wanted_branches(u32 nl, u32 wpv)
+u32 wanted_branches(u32 nl, u32 jobs)
 {
     u64 b = std::max<u64>(2, (48ull << 20) / std::max<u32>(nl, 1));
     if (const char* e = std::getenv("WHARF_BRANCHES")) b = (u64) std::max(1, std::atoi(e));
-    return (u32) std::min<u64>(b, wpv);
+    return (u32) std::max<u64>(1, std::min<u64>(b, jobs));
 }
 
 void plan_buffers(CoalescedPlan& pl, const LaunchCtx& lc, u32 nl, u32 words, u32 branches)
@@ -465,23 +467,42 @@ void plan_buffers(CoalescedPlan& pl, const LaunchCtx& lc, u32 nl, u32 words, u32
     }
 }
 
-// All segments of replica r on the stream of `lc`, with the scratch of branch `b`.
-void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, const CoalescedPlan& pl,
-                     const CoalescedBranch& b, u32 r)
+// One replica's share on this rank: all n walkers (a replica the rank owns entirely) or the walkers of the owned
+// start vertices (a replica sharded over the ranks) - ShardMap, common.cuh.
+struct ReplicaJob
 {
-    const u32 nl = wp.n_local, L = wp.L, words = pl.words;
-    SegmentCtx s{lc, wp, words, div_up(nl, kBlock), div_up(nl, kBlock * kEmitWalkers), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock),
+    u32 replica;      // global replica number (selects the draws)
+    u32 nl;           // walkers
+    u64 first;        // first local walk = column offset in every corpus row
+    u32 rank, world;  // start vertex of walker i: shard_start(i, rank, world, n)
+};
+
+std::vector<ReplicaJob> replica_jobs(const ShardMap& m)
+{
+    std::vector<ReplicaJob> jobs;
+    for (u32 j = 0; j < m.whole; j++) jobs.push_back({m.whole_first + j, (u32) m.n, (u64) j * m.n, 0u, 1u});
+    for (u32 k = 0; k < m.shared; k++) jobs.push_back({m.shared_first + k, m.n_local, m.whole_walks() + (u64) k * m.n_local, m.rank, m.world});
+    return jobs;
+}
+
+// All segments of one replica job on the stream of `lc`, with the scratch of branch `b`.
+void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, const CoalescedPlan& pl,
+                     const CoalescedBranch& b, const ReplicaJob& job)
+{
+    const u32 nl = job.nl, L = wp.L, words = pl.words;
+    if (nl == 0) return;
+    SegmentCtx s{lc, wp, words, nl, div_up(nl, kBlock), div_up(nl, kBlock * kEmitWalkers), grid_for(nl, kBlock, 8, lc.sm_count), div_up(words, kBlock),
                  div_up(words, kTileWords), b.cls.ptr, b.rec.ptr, b.bitmap.ptr, b.word_rank.ptr, b.table.ptr, b.temp.ptr, pl.temp_bytes, d_steps};
     u32 *cv = b.cv_a.ptr, *cv_next = b.cv_b.ptr, *nc = b.counts.ptr, *nc_next = b.counts.ptr + 1;
-    u32* col = wp.walks + (u64) r * nl;                       // column block of the replica in every corpus row
-    coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(b.cls.ptr, cv, col, nl, wp.rank, wp.world, wp.n, nc);
+    u32* col = wp.walks + job.first;                          // column block of the replica in every corpus row
+    coalesced_init_kernel<<<s.walker_grid, kBlock, 0, lc.stream>>>(b.cls.ptr, cv, col, nl, job.rank, job.world, wp.n, nc);
     lc.count();
     for (u32 a = 0; a < L;)
     {
         const u32 R = record_words(a);
         const u32 k = std::min(R - 1, L - a);                 // draws a .. a + k - 1
         SegDraws draws{};
-        for (u32 j = 0; j < k; j++) draws.x[j] = host_draw[(u64) r * L + a + j];
+        for (u32 j = 0; j < k; j++) draws.x[j] = host_draw[(u64) job.replica * L + a + j];
         const u32 stored = std::min(k, L - 1 - a);            // cells a + 1 .. a + stored exist; the last draw is only counted
         const bool merge = a + k < L;
         u32* first_row = col + (u64) (a + 1) * wp.w_local;
@@ -499,19 +520,20 @@ void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_
 
 // One replica after the other on the caller's stream.
 void enqueue_serial(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
-                    const std::function<void(u32)>& after_replica)
+                    const std::vector<ReplicaJob>& jobs, const std::function<void(u64, u64)>& after_replica)
 {
     const CoalescedBranch& b = pl.branch[0];
     WHARF_CUDA(cudaMemsetAsync(b.bitmap.ptr, 0, (u64) pl.words * 4, lc.stream));
-    for (u32 r = 0; r < wp.wpv; r++)
+    for (const ReplicaJob& job : jobs)
     {
-        enqueue_replica(lc, wp, host_draw, d_steps, pl, b, r);
-        if (after_replica) after_replica(r);
+        enqueue_replica(lc, wp, host_draw, d_steps, pl, b, job);
+        if (after_replica) after_replica(job.first, job.nl);
     }
 }
 
-// Inside a stream capture: replica r on branch r % branches; the extra branches fork from and join the caller's stream.
-void enqueue_forked(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl, u32 branches)
+// Inside a stream capture: job j on branch j % branches; the extra branches fork from and join the caller's stream.
+void enqueue_forked(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
+                    const std::vector<ReplicaJob>& jobs, u32 branches)
 {
     WHARF_CUDA(cudaEventRecord(pl.fork, lc.stream));
     for (u32 i = 0; i < branches; i++)
@@ -520,7 +542,7 @@ void enqueue_forked(const LaunchCtx& lc, const WalkParams& wp, const u64* host_d
         LaunchCtx blc = lc;
         if (i) { blc.stream = b.stream; WHARF_CUDA(cudaStreamWaitEvent(b.stream, pl.fork, 0)); }
         WHARF_CUDA(cudaMemsetAsync(b.bitmap.ptr, 0, (u64) pl.words * 4, blc.stream));
-        for (u32 r = i; r < wp.wpv; r += branches) enqueue_replica(blc, wp, host_draw, d_steps, pl, b, r);
+        for (size_t j = i; j < jobs.size(); j += branches) enqueue_replica(blc, wp, host_draw, d_steps, pl, b, jobs[j]);
     }
     for (u32 i = 1; i < branches; i++)
     {
@@ -537,10 +559,13 @@ bool graphs_enabled()
 }  // namespace
 
 void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps,
-                              const std::function<void(u32)>& after_replica, CoalescedPlan** plan_slot)
+                              const std::function<void(u64, u64)>& after_replica, CoalescedPlan** plan_slot)
 {
     if (wp.w_local == 0) return;
     const u32 words = (u32) ((wp.n + 31) / 32);
+    const std::vector<ReplicaJob> jobs = replica_jobs(wp.map);
+    u32 nl_max = 0;
+    for (const ReplicaJob& job : jobs) nl_max = std::max(nl_max, job.nl);
     CoalescedPlan local;
     CoalescedPlan* pl = &local;
     if (plan_slot)
@@ -549,16 +574,17 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
         pl = *plan_slot;
     }
     const bool as_graph = !after_replica && plan_slot && graphs_enabled();
-    const u32 branches = as_graph ? wanted_branches(wp.n_local, wp.wpv) : 1;
-    plan_buffers(*pl, lc, wp.n_local, words, branches);
+    const u32 branches = as_graph ? wanted_branches(nl_max, (u32) jobs.size()) : 1;
+    plan_buffers(*pl, lc, nl_max, words, branches);
     if (!as_graph)
     {
-        enqueue_serial(lc, wp, host_draw, d_steps, *pl, after_replica);
+        enqueue_serial(lc, wp, host_draw, d_steps, *pl, jobs, after_replica);
         return;
     }
     u64 draw_hash = 1469598103934665603ull;
     for (u64 i = 0; i < (u64) wp.wpv * wp.L; i++) draw_hash = (draw_hash ^ host_draw[i]) * 1099511628211ull;
-    const CoalescedPlan::Key key{wp.desc, wp.pool, wp.walks, d_steps, wp.n, wp.w_local, draw_hash, wp.n_local, wp.wpv, wp.L, wp.rank, wp.world};
+    const CoalescedPlan::Key key{wp.desc, wp.pool, wp.walks, d_steps, wp.n, wp.w_local, draw_hash, wp.map.n_local, wp.wpv, wp.L, wp.map.rank, wp.map.world,
+                                 wp.map.whole};
     if (!pl->exec || !(pl->key == key))
     {
         pl->drop_graph();
@@ -570,7 +596,7 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
         WHARF_CUDA(cudaStreamBeginCapture(lc.stream, cudaStreamCaptureModeThreadLocal));
         try
         {
-            enqueue_forked(cap, wp, host_draw, d_steps, *pl, branches);
+            enqueue_forked(cap, wp, host_draw, d_steps, *pl, jobs, branches);
         }
         catch (...)
         {

@@ -84,15 +84,14 @@ __global__ void find_next_kernel(const u64* __restrict__ ptr, const u32* __restr
 
 // code = pair(walk_id * L + position, next)   (walks/compressed_walks.h:52-86 decodes exactly this)
 __global__ void __launch_bounds__(256) encode_codes_kernel(const u32* __restrict__ cells, u64 entries, const u32* __restrict__ walks, u64 w_local,
-                                                           u32 L, u64 n, u32 n_local, u32 rank, u32 world, u64* __restrict__ codes)
+                                                           u32 L, u64 n, ShardMap map, u64* __restrict__ codes)
 {
     const u64 i = (u64) blockIdx.x * 256 + threadIdx.x;
     if (i >= entries) return;
     const u32 cell = cells[i];
     const u32 pos = (u32) (cell / w_local);
     const u64 w = cell - (u64) pos * w_local;
-    const u32 replica = (u32) (w / n_local);
-    const u64 walk_id = (u64) replica * n + shard_start((u32) (w - (u64) replica * n_local), rank, world, n);
+    const u64 walk_id = map.global_id(w);
     u32 next = kRefSentinel;
     if (pos + 1 < L)
     {
@@ -193,12 +192,12 @@ void index_find_next(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_w
     WHARF_CUDA(cudaGetLastError());
 }
 
-void compressed_walks_encode(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u64 n, u32 n_local,
-                             u32 rank, u32 world, u64* d_codes)
+void compressed_walks_encode(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u64 n, const ShardMap& map,
+                             u64* d_codes)
 {
     if (idx.entries == 0) return;
     Scratch<u64> raw(lc.stream, idx.entries);
-    encode_codes_kernel<<<div_up(idx.entries, 256), 256, 0, lc.stream>>>(idx.cells.ptr, idx.entries, d_walks, w_local, L, n, n_local, rank, world, raw.ptr);
+    encode_codes_kernel<<<div_up(idx.entries, 256), 256, 0, lc.stream>>>(idx.cells.ptr, idx.entries, d_walks, w_local, L, n, map, raw.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
     // the reference keeps each vertex's codes as an ordered set (C-tree): sort every segment ascending

@@ -36,9 +36,8 @@ struct DevWalkParams
     u64 n;
     u64 w_local;
     u64 first;                        // first local walk of this launch (bulk generation in chunks)
-    u32 n_local;
+    ShardMap map;                     // local walk -> (replica, start vertex)
     u32 L;
-    u32 rank, world;
     u32 init_strategy;
     float inv_p, inv_q;
     u64 seed;
@@ -77,10 +76,11 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkP
             w   = p.first + t;
             pos = 0;
         }
-        const u32 replica = (u32) (w / p.n_local);                  // = walk_id / n  (wharfmh.h:291)
+        u32 replica, start;                                         // = walk_id / n, walk_id % n  (wharfmh.h:291-292)
+        p.map.locate(w, replica, start);
         if (!kRewalk)
         {
-            cur = shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n);   // = walk_id % n (wharfmh.h:292)
+            cur = start;
             p.walks[w] = cur;
         }
         const u64* __restrict__ X = p.draw + (u64) replica * p.L;   // stream restarts at the re-walk point (:814-816)
@@ -121,9 +121,10 @@ __global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkP
     {
         const u64 w = t + (u64) k * stride;
         alive[k] = w < p.w_local;
-        const u32 replica = alive[k] ? (u32) (w / p.n_local) : 0;
+        u32 replica = 0, start = 0;
+        if (alive[k]) p.map.locate(w, replica, start);
         rep_off[k] = replica * p.L;
-        cur[k] = alive[k] ? shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n) : 0;
+        cur[k] = start;
         if (alive[k]) p.walks[w] = cur[k];
     }
     bool live[kWalks];          // walker still moving (alive and not stopped on a degree-0 vertex)
@@ -347,8 +348,8 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
     if (owner)
     {
         if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = p.first + t; }
-        const u32 replica = (u32) (w / p.n_local);
-        const u32 start = shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n);
+        u32 replica, start;
+        p.map.locate(w, replica, start);
         walk_id = (u64) replica * p.n + start;                       // global id keys the draws
         if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
         else { cur = start; p.walks[w] = cur; }
@@ -460,8 +461,8 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkPar
         u64 w;
         u32 pos = 0, cur;
         if (kRewalk) { w = __ldg(affected + t); pos = __ldg(positions + t); } else { w = p.first + t; }
-        const u32 replica = (u32) (w / p.n_local);
-        const u32 start = shard_start((u32) (w - (u64) replica * p.n_local), p.rank, p.world, p.n);
+        u32 replica, start;
+        p.map.locate(w, replica, start);
         const u64 walk_id = (u64) replica * p.n + start;
         if (kRewalk) cur = p.walks[(u64) pos * p.w_local + w];
         else { cur = start; p.walks[w] = cur; }
@@ -742,7 +743,7 @@ DevWalkParams to_dev(const WalkParams& wp)
 {
     DevWalkParams p;
     p.desc = wp.desc; p.pool = wp.pool; p.version = wp.version; p.pool_rw = wp.pool_rw; p.draw = wp.draw; p.walks = wp.walks;
-    p.n = wp.n; p.w_local = wp.w_local; p.n_local = wp.n_local; p.L = wp.L; p.rank = wp.rank; p.world = wp.world;
+    p.n = wp.n; p.w_local = wp.w_local; p.map = wp.map; p.L = wp.L;
     p.init_strategy = wp.init_strategy;
     p.inv_p = 1 / wp.p;                                                 // node2vec.h:78
     p.inv_q = 1 / wp.q;                                                 // node2vec.h:86

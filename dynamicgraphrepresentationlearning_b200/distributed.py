@@ -2,9 +2,9 @@
 two exchanges the path has.
 
 The reference is single-process; this is the B200 scale-out of the same API.  Walks shard by
-start vertex (one vertex of every block of `world` consecutive ids per rank, rotated from block to block:
-wmh_walk_owner / wmh_local_start_vertices), every rank holds a full replica of the graph, and no collective runs
-while walking.  Per edge batch:
+replica first (walks_per_vertex // world whole replicas per rank) and the remaining replicas by start vertex (one
+vertex of every block of `world` consecutive ids per rank, rotated from block to block: wmh_walk_owner /
+wmh_local_walk_ids), every rank holds a full replica of the graph, and no collective runs while walking.  Per edge batch:
   C1  broadcast of the batch from the source rank (<= 16 MB for 2 M edges), so every replica merges the
       same edges;
   C2  all-gather of the affected walk ids (counts first, then a padded all-gather) so that every rank can

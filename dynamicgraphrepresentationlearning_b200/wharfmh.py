@@ -237,17 +237,11 @@ class WharfMH:
         return int(self._lib.wmh_global_to_local_walk(self._h, walk_id))
 
     def local_walk_ids(self) -> np.ndarray:
-        """Global ids of the local walks in local order (ascending)."""
-        n, wpv = self.number_of_vertices(), self.config.walks_per_vertex
-        starts = self.local_start_vertices().astype(np.uint64)
-        return (np.arange(wpv, dtype=np.uint64)[:, None] * np.uint64(n) + starts[None, :]).reshape(-1)
-
-    def local_start_vertices(self) -> np.ndarray:
-        """Start vertices this rank owns, ascending (the sharding rule of include/wharfmh_b200.h)."""
-        count = int(self._lib.wmh_local_start_vertices(self._h, None, 0))
-        out = np.empty(count, dtype=np.uint32)
+        """Global ids of the local walks in local order (ascending): the sharding rule of include/wharfmh_b200.h."""
+        count = int(self._lib.wmh_local_walk_ids(self._h, None, 0))
+        out = np.empty(count, dtype=np.uint64)
         if count:
-            self._lib.wmh_local_start_vertices(self._h, out.ctypes.data_as(C.c_void_p), count)
+            self._lib.wmh_local_walk_ids(self._h, out.ctypes.data_as(C.c_void_p), count)
         return out
 
     def walk_owner(self, walk_id: int) -> int:

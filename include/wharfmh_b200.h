@@ -16,8 +16,9 @@
  *   - `host` pointers are ordinary (pageable or pinned) host memory; `_device` variants take device
  *     pointers on the engine's device and never touch the host.
  *   - walk ids are GLOBAL ids (walk_id = replica * n + start_vertex, graph/wharfmh.h:275-292); with
- *     world > 1 an engine owns the walks of one start vertex out of every block of `world` consecutive
- *     ids (wmh_walk_owner, wmh_local_start_vertices), the graph is replicated.
+ *     world > 1 an engine owns whole replicas first and, of the remaining replicas, the walks of one start
+ *     vertex out of every block of `world` consecutive ids (wmh_walk_owner, wmh_local_walk_ids); the graph
+ *     is replicated.
  *   - there is no CPU fallback: every call fails with WMH_ERR_CUDA when no sm_100-class device is usable.
  */
 #ifndef WHARFMH_B200_H
@@ -195,13 +196,15 @@ WMH_API int wmh_walks_copy(wmh_engine* e, uint64_t first, uint64_t count, uint32
 WMH_API int wmh_walks_gather(wmh_engine* e, const uint32_t* local_ids, uint64_t count, uint32_t* out);
 WMH_API uint64_t wmh_local_to_global_walk(const wmh_engine* e, uint64_t local_walk);
 WMH_API int64_t  wmh_global_to_local_walk(const wmh_engine* e, uint64_t walk_id);   /* -1 when not owned */
-/* Sharding rule (config.world > 1): vertices are taken in blocks of `world` consecutive ids and every rank owns one
- * vertex of each block, rotated from block to block so that dense and sparse id residues spread evenly.
- * wmh_walk_owner = the rank that owns walk_id (its start vertex is walk_id % n, graph/wharfmh.h:292);
- * wmh_local_start_vertices = the start vertices this rank owns, ascending (local walk i of replica r starts at
- * out[i] and has global id r * n + out[i]); returns their number. */
+/* Sharding rule (config.world > 1).  The walks_per_vertex replicas of the corpus (replica = walk_id / n,
+ * graph/wharfmh.h:291) are independent: with q = walks_per_vertex / world every rank owns q replicas entirely
+ * (replicas [rank * q, rank * q + q)); the remaining walks_per_vertex - world * q replicas are sharded by start
+ * vertex: vertices are taken in blocks of `world` consecutive ids and every rank owns one vertex of each block,
+ * rotated from block to block so that dense and sparse id residues spread evenly.
+ * wmh_walk_owner = the rank that owns walk_id; wmh_local_walk_ids = the global ids of the walks this rank owns, in
+ * local walk order (ascending); returns their number. */
 WMH_API uint32_t wmh_walk_owner(const wmh_engine* e, uint64_t walk_id);
-WMH_API uint64_t wmh_local_start_vertices(const wmh_engine* e, uint32_t* out, uint64_t capacity);
+WMH_API uint64_t wmh_local_walk_ids(const wmh_engine* e, uint64_t* out, uint64_t capacity);
 /* FNV-1a-64 fingerprint of the local corpus in walk() text form (computed on the device). */
 WMH_API int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum_of_row_hashes);
 

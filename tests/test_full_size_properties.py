@@ -61,8 +61,8 @@ def check_walks_are_valid(g, e, keys=None, degree=None):
     degree = g["degree"] if degree is None else degree
     walks = device_corpus(e).to(torch.int64) & 0xFFFFFFFF
     n, w_local = g["n"], walks.shape[1]
-    starts = torch.from_numpy(e.local_start_vertices().astype(np.int64)).to(walks.device)
-    assert torch.equal(walks[0], starts.repeat(WPV)), "a walk does not start at walk_id % n"
+    starts = torch.from_numpy((e.local_walk_ids() % np.uint64(g["n"])).astype(np.int64)).to(walks.device)
+    assert torch.equal(walks[0], starts), "a walk does not start at walk_id % n"
     bad = 0
     for p in range(LEN - 1):
         a, b = walks[p], walks[p + 1]

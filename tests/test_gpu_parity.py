@@ -266,29 +266,34 @@ def test_sharded_corpus_equals_global(wharf, wo):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,world", [(512, 2), (509, 3), (1000, 8), (7, 8), (64, 5)])
-def test_shard_rule_is_a_partition(wharf, n, world):
-    """Every vertex is the start vertex of exactly one rank, ascending per rank, consistent with wmh_walk_owner and
-    with the local <-> global walk id maps; rank r owns ceil((n - r) / world) starts."""
+@pytest.mark.parametrize("n,world,wpv", [(512, 2, 2), (509, 3, 2), (1000, 8, 10), (7, 8, 3), (64, 5, 10), (300, 4, 10), (129, 2, 5)])
+def test_shard_rule_is_a_partition(wharf, n, world, wpv):
+    """Every walk has exactly one owner: whole replicas first (wpv // world per rank), the remaining replicas by start
+    vertex (one vertex per block of `world` ids and rank, rotated per block).  Local order = ascending global id,
+    consistent with wmh_walk_owner and the local <-> global maps."""
     off = np.zeros(n, dtype=np.uint64)
     adj = np.zeros(0, dtype=np.uint32)
-    seen = np.full(n, -1, dtype=np.int64)
+    owner = np.full(n * wpv, -1, dtype=np.int64)
+    q = wpv // world
     for r in range(world):
-        with make(wharf, n, off, adj, walks_per_vertex=2, walk_length=3, rank=r, world=world) as e:
-            starts = e.local_start_vertices().astype(np.int64)
-            assert starts.shape[0] == (n - r + world - 1) // world if r < n else starts.shape[0] == 0
-            assert (np.diff(starts) > 0).all()
-            assert (seen[starts] == -1).all()
-            seen[starts] = r
-            assert all(e.walk_owner(int(v)) == r and e.walk_owner(int(n + v)) == r for v in starts[:50])
+        with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=3, rank=r, world=world) as e:
+            ids = e.local_walk_ids().astype(np.int64)
+            starts_per_shared = (n - r + world - 1) // world if r < n else 0
+            assert ids.shape[0] == e.number_of_local_walks() == q * n + (wpv - world * q) * starts_per_shared
+            assert (np.diff(ids) > 0).all()
+            assert (owner[ids] == -1).all()
+            owner[ids] = r
+            whole = ids[: q * n]
+            assert np.array_equal(whole, np.arange(r * q * n, (r + 1) * q * n))
+            assert all(e.walk_owner(int(g)) == r for g in ids[:: max(1, ids.shape[0] // 64)])
             e.generate_initial_random_walks()
-            ids = e.local_walk_ids()
-            assert np.array_equal(ids[: starts.shape[0]], starts.astype(np.uint64))
-            assert all(e.global_to_local_walk(int(g)) == i for i, g in enumerate(ids[:40]))
-            assert np.array_equal(e.walks()[:, 0], (ids % np.uint64(n)).astype(np.uint32))
-    assert (seen >= 0).all()
+            assert np.array_equal(e.local_walk_ids().astype(np.int64), ids)
+            assert all(e.global_to_local_walk(int(g)) == i for i, g in list(enumerate(ids))[:: max(1, ids.shape[0] // 64)])
+            assert np.array_equal(e.walks()[:, 0], (ids % n).astype(np.uint32))
+    assert (owner >= 0).all()
     if world == 8 and n == 1000:
-        assert len({int(seen[b * 8]) for b in range(100)}) > 1          # rotated from block to block
+        shared = owner[8 * n: 9 * n]                                   # replica 8 is sharded by start vertex
+        assert len({int(shared[b * 8]) for b in range(100)}) > 1       # rotated from block to block
 
 
 @pytest.mark.gpu

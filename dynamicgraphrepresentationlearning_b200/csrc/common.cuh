@@ -172,20 +172,26 @@ __host__ __device__ __forceinline__ u32 shard_owner(u32 vertex, u32 world, u64 n
 }
 
 // Which walks a rank owns.  Replicas (walk_id / n) are independent, so whole replicas go first: with q = wpv / world
-// every rank owns the q replicas [rank * q, rank * q + q) entirely (all n start vertices); the remaining wpv - world * q
-// replicas are sharded by start vertex (shard_start above).  Whole replicas keep the deterministic coalesced schedule
-// at its single-GPU efficiency (the walkers of a replica merge as on one GPU); wpv < world degenerates to pure start-
-// vertex sharding, wpv % world == 0 to pure replica sharding.  Local walk order: the whole replicas (start ascending),
-// then the sharded ones (owned starts ascending), i.e. ascending global walk id.
+// every rank owns the q replicas [rank * q, rank * q + q) entirely (all n start vertices).  The remaining
+// R = wpv - world * q replicas are shared out in g = gcd(world, R) groups of world / g ranks: group k shards the R / g
+// replicas [world * q + k * R / g, ...) by start vertex among its ranks (shard_start above, with the rank's position
+// in its group).  So at wpv = 10: 2 ranks own 5 replicas each; 4 ranks 2 replicas + half of one more; 8 ranks 1
+// replica + a quarter of one more.  Fewer, larger shares matter to the deterministic coalesced schedule: the walkers
+// of a replica merge, so a quarter of one replica costs less than two eighths of two (measured);
+// wpv < world with gcd 1 degenerates to pure start-vertex sharding, wpv % world == 0 to pure replica sharding.
+// Local walk order: the whole replicas (start ascending), then the shared ones (owned starts ascending), i.e.
+// ascending global walk id.
 struct ShardMap
 {
     u64 n = 0;                // vertices
     u32 rank = 0, world = 1;
     u32 whole = 0;            // replicas owned entirely
     u32 whole_first = 0;      // first of them (global replica number)
-    u32 shared = 0;           // replicas sharded by start vertex
+    u32 shared_base = 0;      // first replica that is not owned whole by anyone (= world * q)
+    u32 shared = 0;           // shared replicas this rank's group works on
     u32 shared_first = 0;     // first of them
-    u32 n_local = 0;          // start vertices this rank owns in a sharded replica
+    u32 sub_rank = 0, sub_world = 1;   // position in / size of the group
+    u32 n_local = 0;          // start vertices this rank owns in a shared replica
 
     __host__ __device__ u64 whole_walks() const { return (u64) whole * n; }
     __host__ __device__ u64 local_walks() const { return whole_walks() + (u64) shared * n_local; }
@@ -204,7 +210,7 @@ struct ShardMap
             const u64 x = w - ww;
             const u32 r = (u32) (x / n_local);
             replica = shared_first + r;
-            start = shard_start((u32) (x - (u64) r * n_local), rank, world, n);
+            start = shard_start((u32) (x - (u64) r * n_local), sub_rank, sub_world, n);
         }
     }
     __host__ __device__ u64 global_id(u64 w) const
@@ -217,8 +223,9 @@ struct ShardMap
     __host__ __device__ u32 owner(u64 walk_id) const
     {
         const u32 replica = (u32) (walk_id / n);
-        if (replica < shared_first) return whole ? replica / whole : 0u;      // every rank owns the same number of whole replicas
-        return shard_owner((u32) (walk_id % n), world, n);
+        if (replica < shared_base) return whole ? replica / whole : 0u;       // every rank owns the same number of whole replicas
+        const u32 group = shared ? (replica - shared_base) / shared : 0u;     // every group works on the same number
+        return group * sub_world + shard_owner((u32) (walk_id % n), sub_world, n);
     }
     // local index of an owned global walk id, -1 otherwise
     __host__ __device__ i64 local_of(u64 walk_id) const
@@ -226,8 +233,8 @@ struct ShardMap
         if (owner(walk_id) != rank) return -1;
         const u32 replica = (u32) (walk_id / n);
         const u32 start = (u32) (walk_id % n);
-        if (replica < shared_first) return (i64) ((u64) (replica - whole_first) * n + start);
-        return (i64) (whole_walks() + (u64) (replica - shared_first) * n_local + start / world);
+        if (replica < shared_base) return (i64) ((u64) (replica - whole_first) * n + start);
+        return (i64) (whole_walks() + (u64) (replica - shared_first) * n_local + start / sub_world);
     }
 };
 
@@ -237,12 +244,19 @@ inline ShardMap make_shard_map(u64 n, u32 wpv, u32 rank, u32 world)
     m.n = n;
     m.rank = rank;
     m.world = world;
-    const u32 q = world > 1 ? wpv / world : 0;       // one rank: everything is "sharded" over a world of one
+    const u32 q = world > 1 ? wpv / world : 0;       // one rank: everything is "shared" by a group of one
     m.whole = q;
     m.whole_first = rank * q;
-    m.shared_first = world > 1 ? world * q : 0;
-    m.shared = wpv - m.shared_first;
-    m.n_local = rank < n ? (u32) ((n - rank + world - 1) / world) : 0;
+    m.shared_base = world > 1 ? world * q : 0;
+    const u32 rest = wpv - m.shared_base;
+    u32 g = world, b = rest;                         // gcd(world, rest); gcd(world, 0) = world
+    while (b) { const u32 t = g % b; g = b; b = t; }
+    if (rest == 0) g = world;
+    m.sub_world = world / g;
+    m.sub_rank = rank % m.sub_world;
+    m.shared = rest / g;
+    m.shared_first = m.shared_base + (rank / m.sub_world) * m.shared;
+    m.n_local = m.sub_rank < n ? (u32) ((n - m.sub_rank + m.sub_world - 1) / m.sub_world) : 0;
     return m;
 }
 

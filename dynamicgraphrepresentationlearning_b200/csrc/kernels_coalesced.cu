@@ -425,7 +425,7 @@ namespace
 // 78.6 -> 73.9 ms on one GPU with 2 branches, 23.8 -> 19.4 ms on a shard of eight with 5+).  WHARF_BRANCHES overrides.
 u32 wanted_branches(u32 nl, u32 jobs)
 {
-    u64 b = std::max<u64>(2, (48ull << 20) / std::max<u32>(nl, 1));
+    u64 b = std::max<u64>(jobs <= 3 ? 3 : 2, (48ull << 20) / std::max<u32>(nl, 1));
     if (const char* e = std::getenv("WHARF_BRANCHES")) b = (u64) std::max(1, std::atoi(e));
     return (u32) std::max<u64>(1, std::min<u64>(b, jobs));
 }
@@ -481,7 +481,7 @@ std::vector<ReplicaJob> replica_jobs(const ShardMap& m)
 {
     std::vector<ReplicaJob> jobs;
     for (u32 j = 0; j < m.whole; j++) jobs.push_back({m.whole_first + j, (u32) m.n, (u64) j * m.n, 0u, 1u});
-    for (u32 k = 0; k < m.shared; k++) jobs.push_back({m.shared_first + k, m.n_local, m.whole_walks() + (u64) k * m.n_local, m.rank, m.world});
+    for (u32 k = 0; k < m.shared; k++) jobs.push_back({m.shared_first + k, m.n_local, m.whole_walks() + (u64) k * m.n_local, m.sub_rank, m.sub_world});
     return jobs;
 }
 
@@ -584,7 +584,7 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
     u64 draw_hash = 1469598103934665603ull;
     for (u64 i = 0; i < (u64) wp.wpv * wp.L; i++) draw_hash = (draw_hash ^ host_draw[i]) * 1099511628211ull;
     const CoalescedPlan::Key key{wp.desc, wp.pool, wp.walks, d_steps, wp.n, wp.w_local, draw_hash, wp.map.n_local, wp.wpv, wp.L, wp.map.rank, wp.map.world,
-                                 wp.map.whole};
+                                 wp.map.whole * 65536u + wp.map.shared_first};
     if (!pl->exec || !(pl->key == key))
     {
         pl->drop_graph();

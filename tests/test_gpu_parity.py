@@ -268,9 +268,10 @@ def test_sharded_corpus_equals_global(wharf, wo):
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,world,wpv", [(512, 2, 2), (509, 3, 2), (1000, 8, 10), (7, 8, 3), (64, 5, 10), (300, 4, 10), (129, 2, 5)])
 def test_shard_rule_is_a_partition(wharf, n, world, wpv):
-    """Every walk has exactly one owner: whole replicas first (wpv // world per rank), the remaining replicas by start
-    vertex (one vertex per block of `world` ids and rank, rotated per block).  Local order = ascending global id,
-    consistent with wmh_walk_owner and the local <-> global maps."""
+    """Every walk has exactly one owner: whole replicas first (wpv // world per rank); the remaining replicas go to
+    gcd(world, rest) groups of ranks, sharded by start vertex inside a group (one vertex per block of group-size ids and
+    rank, rotated per block).  Local order = ascending global id, consistent with wmh_walk_owner and the maps."""
+    import math
     off = np.zeros(n, dtype=np.uint64)
     adj = np.zeros(0, dtype=np.uint32)
     owner = np.full(n * wpv, -1, dtype=np.int64)
@@ -278,8 +279,12 @@ def test_shard_rule_is_a_partition(wharf, n, world, wpv):
     for r in range(world):
         with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=3, rank=r, world=world) as e:
             ids = e.local_walk_ids().astype(np.int64)
-            starts_per_shared = (n - r + world - 1) // world if r < n else 0
-            assert ids.shape[0] == e.number_of_local_walks() == q * n + (wpv - world * q) * starts_per_shared
+            rest = wpv - world * q
+            g = math.gcd(world, rest) if rest else world
+            sub_world, shared = world // g, rest // g
+            sub_rank = r % sub_world
+            starts_per_shared = (n - sub_rank + sub_world - 1) // sub_world if sub_rank < n else 0
+            assert ids.shape[0] == e.number_of_local_walks() == q * n + shared * starts_per_shared
             assert (np.diff(ids) > 0).all()
             assert (owner[ids] == -1).all()
             owner[ids] = r
@@ -292,8 +297,9 @@ def test_shard_rule_is_a_partition(wharf, n, world, wpv):
             assert np.array_equal(e.walks()[:, 0], (ids % n).astype(np.uint32))
     assert (owner >= 0).all()
     if world == 8 and n == 1000:
-        shared = owner[8 * n: 9 * n]                                   # replica 8 is sharded by start vertex
-        assert len({int(shared[b * 8]) for b in range(100)}) > 1       # rotated from block to block
+        shared = owner[8 * n: 9 * n]                                   # replica 8 is sharded among ranks 0..3
+        assert set(shared.tolist()) == {0, 1, 2, 3} and set(owner[9 * n:].tolist()) == {4, 5, 6, 7}
+        assert len({int(shared[b * 4]) for b in range(100)}) > 1       # rotated from block to block
 
 
 @pytest.mark.gpu

@@ -54,28 +54,63 @@ def log(*a):
 # clocks: sample nvidia-smi during the timed region
 # ----------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons DURING the timed region: NVML polled every 5 ms from a thread (the timed region of the
+    default run is ~150 ms, one nvidia-smi process launch would not fit into it); nvidia-smi when NVML is unavailable."""
     FIELDS = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.samples: list[list[str]] = []
+        self.sm: list[int] = []
+        self.max_sm = None
+        self.reasons: set[str] = set()
+        self.source = "nvml"
         self._stop = threading.Event()
         self._thread = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            physical = int(visible.split(",")[gpu_index]) if visible and all(x.strip().isdigit() for x in visible.split(",")) else gpu_index
+            self._handle = pynvml.nvmlDeviceGetHandleByIndex(physical)
+            self.max_sm = int(pynvml.nvmlDeviceGetMaxClockInfo(self._handle, pynvml.NVML_CLOCK_SM))
+            self._nvml = pynvml
+        except Exception:
+            self.source = "nvidia-smi"
 
-    def _run(self):
+    def _poll_nvml(self):
+        nv = self._nvml
+        masks = [(nv.nvmlClocksEventReasonHwSlowdown, "hw_slowdown"), (nv.nvmlClocksEventReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                 (nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_thermal_slowdown"), (nv.nvmlClocksEventReasonSwPowerCap, "sw_power_cap")]
+        while not self._stop.is_set():
+            try:
+                self.sm.append(int(nv.nvmlDeviceGetClockInfo(self._handle, nv.NVML_CLOCK_SM)))
+                bits = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._handle))
+                self.reasons.update(name for mask, name in masks if bits & mask)
+            except Exception:
+                pass
+            self._stop.wait(0.005)
+
+    def _poll_smi(self):
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits"],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
                 if out:
-                    self.samples.append([x.strip() for x in out.splitlines()[0].split(",")])
+                    f = [x.strip() for x in out.splitlines()[0].split(",")]
+                    if f[0].isdigit():
+                        self.sm.append(int(f[0]))
+                    if len(f) > 1 and f[1].isdigit():
+                        self.max_sm = int(f[1])
+                    self.reasons.update(self.NAMES[i] for i in range(4) if len(f) > 2 + i and f[2 + i].lower().startswith("active"))
             except Exception:
                 pass
             self._stop.wait(0.2)
 
     def __enter__(self):
-        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread = threading.Thread(target=self._poll_nvml if self._nvml else self._poll_smi, daemon=True)
         self._thread.start()
         return self
 
@@ -84,12 +119,8 @@ class ClockSampler:
         self._thread.join(timeout=6)
 
     def summary(self) -> dict:
-        sm = [int(s[0]) for s in self.samples if s and s[0].isdigit()]
-        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for s in self.samples for i in range(4) if len(s) > 2 + i and s[2 + i].lower().startswith("active")})
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.max_sm, "reasons": sorted(self.reasons),
+                "samples": len(self.sm), "source": self.source}
 
 
 # ----------------------------------------------------------------------------------------------------

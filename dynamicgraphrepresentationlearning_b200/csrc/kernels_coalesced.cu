@@ -325,6 +325,13 @@ struct SegmentCtx
     unsigned long long* d_steps;
 };
 
+// WHARF_RANK_SCAN=1 takes the library-scan ranking at any size (it is otherwise only reached beyond 134 M vertices).
+bool force_library_scan()
+{
+    const char* e = std::getenv("WHARF_RANK_SCAN");
+    return e && std::atoi(e) != 0;
+}
+
 template <u32 R>
 void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* cv, u32* cv_next, const u32* nc, u32* nc_next, u32* first_row, u32 stored,
                  bool merge)
@@ -334,7 +341,7 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
     lc.count();
     if (merge)
     {
-        if (s.tiles <= kMaxTiles)
+        if (s.tiles <= kMaxTiles && !force_library_scan())
         {
             coalesced_tile_counts_kernel<<<s.tiles, kBlock, 0, lc.stream>>>(s.bitmap, s.words, s.word_rank);
             coalesced_expand_kernel<<<s.tiles, kBlock, 0, lc.stream>>>(s.bitmap, s.word_rank, s.words, s.table, cv_next, nc_next);
@@ -553,8 +560,8 @@ void enqueue_forked(const LaunchCtx& lc, const WalkParams& wp, const u64* host_d
 
 bool graphs_enabled()
 {
-    static const bool on = [] { const char* e = std::getenv("WHARF_GRAPH"); return !e || std::atoi(e) != 0; }();
-    return on;
+    const char* e = std::getenv("WHARF_GRAPH");
+    return !e || std::atoi(e) != 0;
 }
 }  // namespace
 

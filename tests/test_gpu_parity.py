@@ -518,6 +518,25 @@ def test_coalesced_generation_equals_oracle(wharf, wo, case):
         assert np.array_equal(full, o2.walks())
 
 
+@pytest.mark.parametrize("knobs", [{"WHARF_RANK_SCAN": "1"}, {"WHARF_GRAPH": "0"}, {"WHARF_BRANCHES": "1"}, {"WHARF_BRANCHES": "7"}])
+def test_coalesced_schedule_variants(wharf, wo, knobs, monkeypatch):
+    """The corpus does not depend on how the coalesced pass is scheduled: library-scan ranking (the path for more than
+    134 M vertices), plain launches instead of the captured CUDA graph, one or many parallel graph branches."""
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    n = 1 << 11
+    off, adj = wo.rmat_graph(11, 12000, seed=3)
+    o = wo.Oracle(n, off, adj, walks_per_vertex=10, walk_length=80)
+    steps = o.generate()
+    for rank, world in ((0, 1), (1, 4)):
+        with make(wharf, n, off, adj, walks_per_vertex=10, walk_length=80, generate_mode=wharf.GENERATE_COALESCED, rank=rank, world=world) as e:
+            for _ in range(2):                                   # the second pass replays the captured graph
+                got = e.generate_initial_random_walks()
+                assert np.array_equal(e.walks(), o.walks()[e.local_walk_ids().astype(np.int64)])
+            if world == 1:
+                assert got == steps
+
+
 @pytest.mark.parametrize("mode", ["det_walker", "det_coalesced", "n2v_mh", "deepwalk_mh", "sharded"])
 def test_generate_to_host_equals_generate_then_copy(wharf, wo, mode):
     """wmh_generate_initial_random_walks_to_host (generation overlapped with the export) must deliver the corpus that

@@ -1,5 +1,9 @@
 set -x
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-for rw in "0 8" "7 8" "0 4" "3 4"; do python tools/det_modes.py dw25 3 coalesced $rw > gpurun_out/f_det.txt 2>&1; cat gpurun_out/f_det.txt; done
-WHARF_BRANCHES=2 python tools/det_modes.py dw25 3 coalesced 0 8 2>&1 | tail -1
+python bench.py > gpurun_out/p_bench_n2v20.json 2> gpurun_out/p_bench_n2v20.err; tail -c 300 gpurun_out/p_bench_n2v20.err
+python - <<EOF2
+import json
+d = json.loads([l for l in open("gpurun_out/p_bench_n2v20.json") if l.startswith("{")][-1])
+print(d["value"] / 1e9, d["ms_per_step"], d["clocks"], d["index_build_ms"], d["e2e"]["value"] / 1e9, d["gpu_launches"])
+EOF2

@@ -373,24 +373,29 @@ void generate(wmh_engine& e, u32* host_out = nullptr)
     bool exchanged = false;
     if (needs_memo(e))
     {
-        // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90): every cache is emptied, or - with
-        // peers - overwritten by the value its first touch would compute (every state belongs to one rank's share)
-        if (peer_usable(e))
+        // a fresh corpus starts from empty sampler managers (wharfmh.h:41,83,90): every cache is emptied, or overwritten
+        // by the value its first touch would compute.  The bulk kernel pays for every state of the graph, so it is used
+        // when the corpus is large enough to touch most of them anyway (the quantity compared is the same on every
+        // rank: the ranks of a box must take the same branch, they meet at a barrier): with peers each rank computes
+        // 1 / world of the states; on one rank it replaces first-touch inits scattered through the walk kernel
+        // (scale-20: 30.0 -> 29.3 ms).  WHARF_EAGER_INIT=0 keeps the single-rank pass lazy.
+        const u64 steps_per_rank = e.g.n * (u64) wpv * L / e.cfg.world;
+        const char* eager_env = std::getenv("WHARF_EAGER_INIT");
+        if (peer_usable(e) && steps_per_rank >= 2 * e.g.m)
         {
             n2v_share_sampler_init(lc, walk_params(e), e.g.m, e.peer);
             exchanged = true;
         }
-        else graph_aux_clear_caches(lc, e.g);
-        if (!exchanged && e.cfg.world == 1 && std::getenv("WHARF_EAGER_INIT") && std::atoi(std::getenv("WHARF_EAGER_INIT")))
+        else if (e.cfg.world == 1 && steps_per_rank >= 8 * e.g.m && !(eager_env && std::atoi(eager_env) == 0))
         {
-            // tuning aid: the same bulk kernel on one rank (every state initialised up front instead of at first touch)
-            Scratch<u8> flags(e.stream, kPeerFlagBytes);
+            Scratch<u8> flags(e.stream, kPeerFlagBytes);                 // a world of one: the barrier only needs its flag page
             WHARF_CUDA(cudaMemsetAsync(flags.ptr, 0, kPeerFlagBytes, e.stream));
             PeerLink solo;
             solo.ptrs.buf[0] = flags.ptr;
             solo.bytes = kPeerFlagBytes;
             n2v_share_sampler_init(lc, walk_params(e), e.g.m, solo);
         }
+        else graph_aux_clear_caches(lc, e.g);
     }
     if (host_out) generate_and_export(e, host_out);
     else if (use_coalesced(e)) walks_generate_coalesced(lc, walk_params(e), e.host_draw.data(), e.d_steps.ptr, nullptr, &e.coalesced_plan);

@@ -288,20 +288,33 @@ __device__ __forceinline__ InitValue n2v_init_weight_group(const DevWalkParams& 
             fh[k] = filter_hash(x[k]);
             fw[k] = dprev.degree ? __ldcg(aux + filter_block(fh[k], dprev.degree)) >> 16 : 0u;
         }
+        // classes: return / far are decided by the filter alone; the few proposals the filter cannot rule out (common
+        // neighbours and 2.5 % false positives) are searched afterwards, one per lane and trip - the search is a
+        // chain of dependent loads, and a warp that branched into it once per proposal ran it three times per round
+        u32 cls0 = kClassFar, cls1 = kClassFar, cls2 = kClassFar, pending = 0;
+#pragma unroll
+        for (u32 k = 0; k < 3; k++)
+        {
+            if (sub + 8 * k >= 21) break;
+            const u32 need = filter_bits(fh[k]);
+            if (x[k] == prev) { if (k == 0) cls0 = kClassReturn; else if (k == 1) cls1 = kClassReturn; else cls2 = kClassReturn; }
+            else if (dprev.degree && (fw[k] & need) == need) pending |= 1u << k;
+        }
+        while (pending)
+        {
+            const u32 k = (u32) __ffs(pending) - 1u;
+            pending &= pending - 1u;
+            const u32 xk = k == 0 ? x[0] : (k == 1 ? x[1] : x[2]);
+            bool hit;
+            row_find(p.pool + dprev.begin, dprev.degree, xk, &hit);
+            if (hit) { if (k == 0) cls0 = kClassNeighbour; else if (k == 1) cls1 = kClassNeighbour; else cls2 = kClassNeighbour; }
+        }
 #pragma unroll
         for (u32 k = 0; k < 3; k++)
         {
             const u32 i = sub + 8 * k;
             if (i >= 21) break;
-            u32 cls = kClassFar;
-            const u32 need = filter_bits(fh[k]);
-            if (x[k] == prev) cls = kClassReturn;
-            else if (dprev.degree && (fw[k] & need) == need)
-            {
-                bool hit;
-                row_find(p.pool + dprev.begin, dprev.degree, x[k], &hit);
-                if (hit) cls = kClassNeighbour;
-            }
+            const u32 cls = k == 0 ? cls0 : (k == 1 ? cls1 : cls2);
             const float wk = class_weight(p, cls);
             if (wk > w) { w = wk; word = (cls << 30) | slot[k]; idx = i; }
         }

@@ -437,6 +437,31 @@ def test_keyed_mh_mode_vs_oracle(wharf, wo, model, init):
     assert not np.array_equal(o2.walks(), o.walks()) or True
 
 
+@pytest.mark.parametrize("init", ["weight", "random", "burnin"])
+@pytest.mark.parametrize("eager", ["1", "0"])
+def test_bulk_sampler_init_equals_first_touch(wharf, wo, init, eager, monkeypatch):
+    """A corpus large enough to touch most sampler states initialises them with the bulk kernel before walking
+    (n * wpv * L >= 8 m); WHARF_EAGER_INIT=0 keeps the first-touch path.  Same corpus, bit for bit, as the oracle."""
+    monkeypatch.setenv("WHARF_EAGER_INIT", eager)
+    n = 1 << 8
+    off, adj = wo.rmat_graph(8, 1500, seed=4)
+    ini = {"weight": wo.INIT_WEIGHT, "random": wo.INIT_RANDOM, "burnin": wo.INIT_BURNIN}[init]
+    kw = dict(walks_per_vertex=10, walk_length=40)
+    assert n * 10 * 40 >= 8 * adj.shape[0]
+    o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, init_strategy=ini, seed=21, **kw)
+    with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False,
+              sampler_init_strategy=ini, seed=21, **kw) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        assert np.array_equal(e.walks(), o.walks())
+        b = wo.generate_batch(20, n, 2, False, False)
+        o.update(b, delete=False, remove_dups=True)
+        e.insert_edges_batch(b.copy(), remove_dups=True)
+        assert np.array_equal(e.walks(), o.walks())
+        e.destroy_index()
+        assert e.generate_initial_random_walks() == o.generate()          # a fresh corpus on the updated graph
+        assert np.array_equal(e.walks(), o.walks())
+
+
 @pytest.mark.parametrize("init", ["weight", "random"])
 def test_keyed_mh_directed_batches_vs_oracle(wharf, wo, init):
     """node2vec MH with DIRECTED insert/delete batches (no reverse edges): the sampler cache must stay equal to a

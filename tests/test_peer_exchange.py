@@ -29,7 +29,7 @@ def _worker(rank, world, port, out_dir):
         for scale, edges, init in ((9, 4000, wo.INIT_WEIGHT), (12, 40000, wo.INIT_WEIGHT), (9, 4000, wo.INIT_RANDOM), (8, 1500, wo.INIT_BURNIN)):
             n = 1 << scale
             off, adj = wo.rmat_graph(scale, edges, seed=11)
-            kw = dict(walks_per_vertex=3, walk_length=15)
+            kw = dict(walks_per_vertex=10, walk_length=40)      # large enough a corpus for the exchange to be worth it (engine rule)
             o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, init_strategy=init, seed=77, **kw)
             cfg = wharf.Config(random_walk_model=wharf.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False,
                                sampler_init_strategy=init, seed=77, device=rank, rank=rank, world=world, **kw)
@@ -66,10 +66,10 @@ def _worker(rank, world, port, out_dir):
         # the wrapper connects its ranks itself
         n = 1 << 9
         off, adj = wo.rmat_graph(9, 4000, seed=5)
-        cfg = wharf.Config(walks_per_vertex=2, walk_length=12, random_walk_model=wharf.NODE2VEC, paramP=0.7, paramQ=0.2,
+        cfg = wharf.Config(walks_per_vertex=10, walk_length=30, random_walk_model=wharf.NODE2VEC, paramP=0.7, paramQ=0.2,
                            deterministic_mode=False, seed=5, device=rank)
         sharded = ShardedWharfMH(n, int(adj.shape[0]), off, adj, config=cfg)
-        o = wo.Oracle(n, off, adj, walks_per_vertex=2, walk_length=12, model=wo.NODE2VEC, p=0.7, q=0.2, deterministic=False, seed=5)
+        o = wo.Oracle(n, off, adj, walks_per_vertex=10, walk_length=30, model=wo.NODE2VEC, p=0.7, q=0.2, deterministic=False, seed=5)
         assert sharded.generate_initial_random_walks() == o.generate()
         gids, rows = sharded.local_walks()
         assert np.array_equal(rows, o.walks()[gids.astype(np.int64)])
@@ -81,6 +81,16 @@ def _worker(rank, world, port, out_dir):
         gids, rows = sharded.local_walks()
         assert np.array_equal(rows, o.walks()[gids.astype(np.int64)])
         sharded.destroy()
+        # a corpus too small to touch most sampler states keeps the lazy first-touch init (no exchange, same corpus)
+        cfg = wharf.Config(walks_per_vertex=1, walk_length=4, random_walk_model=wharf.NODE2VEC, paramP=0.7, paramQ=0.2,
+                           deterministic_mode=False, seed=5, device=rank)
+        tiny = ShardedWharfMH(n, int(adj.shape[0]), off, adj, config=cfg)
+        o = wo.Oracle(n, off, adj, walks_per_vertex=1, walk_length=4, model=wo.NODE2VEC, p=0.7, q=0.2, deterministic=False, seed=5)
+        assert tiny.generate_initial_random_walks() == o.generate()
+        gids, rows = tiny.local_walks()
+        assert np.array_equal(rows, o.walks()[gids.astype(np.int64)])
+        assert tiny.engine.peer_exchanges() == 0
+        tiny.destroy()
         (Path(out_dir) / f"ok{rank}").write_text("True")
     finally:
         dist.destroy_process_group()

@@ -348,7 +348,8 @@ def main():
         kernel_name = ("coalesced_{advance,tile_counts,expand,relabel,emit}_kernel segments (kernels_coalesced.cu), one generate pass replayed as a CUDA graph" if coalesced
                        else "walk_deterministic_ilp_kernel<1,256,0>")
     else:
-        kernel_name = "walk_n2v_kernel<false>" if spec["model"] == "node2vec" else "walk_deepwalk_mh_kernel<false>"
+        kernel_name = ("walk_n2v_kernel<false> (+ n2v_share_init_kernel: bulk sampler init, 16 % of the pass)" if spec["model"] == "node2vec"
+                       else "walk_deepwalk_mh_kernel<false>")
     steps_per_launch = local_steps / args.steps
     achieved_gbs = steps_per_launch * bytes_per_step / (kernel_avg_ms * 1e-3) / 1e9
     traffic = None
@@ -361,7 +362,8 @@ def main():
                 # the bound the north star names: random 32-B sector gathers from HBM, measured with tools/gather_probe.cu
                 # (profiles/r01c_gather_probe.txt): 37.7 G sectors/s from a 4 GiB table, whatever the policy or occupancy
                 "random_gather": {"peak_gsectors_s": 37.7, "source": "tools/gather_probe.cu, profiles/r01c_gather_probe.txt",
-                                  "dram_fetches_per_s_64B": (traffic["read"] / 64 / (kernel_avg_ms * 1e-3)) if isinstance(traffic, dict) else None}}
+                                  "dram_fetches_per_s_64B": (traffic["read"] / 64 / (traffic.get("kernel_ms", kernel_avg_ms) * 1e-3)) if isinstance(traffic, dict) else None,
+                                  "note": "fetch rate = ncu DRAM bytes read / 64 B over the ncu duration of the walk kernel alone"}}
     if isinstance(traffic, dict):
         roofline["traffic"] = traffic["read"] + traffic["write"]
 

@@ -268,6 +268,19 @@ __device__ __forceinline__ u32 filter_hash(u32 x)
 __device__ __forceinline__ u32 filter_block(u32 h, u32 degree) { return __umulhi(h, degree); }
 __device__ __forceinline__ u32 filter_bits(u32 h) { return (1u << (h & 15)) | (1u << ((h >> 4) & 15)); }
 
+// lower_bound over an ascending row whose element i sits at a[i << shift] (shift 1: neighbours interleaved with their
+// aux words, kernels_graph.cu).
+__device__ __forceinline__ u32 lower_bound_row(const u32* __restrict__ a, u32 n, u32 key, u32 shift)
+{
+    u32 lo = 0, hi = n;
+    while (lo < hi)
+    {
+        u32 mid = (lo + hi) >> 1;
+        if (__ldg(a + ((u64) mid << shift)) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
 // lower_bound over an ascending u32 array slice.
 __device__ __forceinline__ u32 lower_bound_u32(const u32* __restrict__ a, u32 n, u32 key)
 {

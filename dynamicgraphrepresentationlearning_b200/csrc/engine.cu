@@ -221,6 +221,7 @@ WalkParams walk_params(wmh_engine& e)
     wp.pool = e.g.pool.ptr;
     wp.version = e.g.version.ptr;
     wp.pool_rw = e.g.tail ? e.g.pool.ptr : nullptr;
+    wp.shift = e.g.tail;
     wp.draw = e.draw.ptr;
     wp.walks = e.walks.ptr;
     wp.n = e.g.n;
@@ -772,7 +773,9 @@ int wmh_neighbors(wmh_engine* e, uint32_t vertex, uint32_t* out, uint64_t capaci
         if (out)
         {
             if (capacity < d.degree) return fail(WMH_ERR_RANGE, "neighbour buffer too small");
-            if (d.degree) WHARF_CUDA(cudaMemcpyAsync(out, e->g.pool.ptr + d.begin, d.degree * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+            // neighbour i sits at begin + (i << tail): a strided copy when the row is interleaved with aux words
+            if (d.degree) WHARF_CUDA(cudaMemcpy2DAsync(out, sizeof(u32), e->g.pool.ptr + d.begin, sizeof(u32) << e->g.tail, sizeof(u32), d.degree,
+                                                       cudaMemcpyDeviceToHost, e->stream));
             WHARF_CUDA(cudaStreamSynchronize(e->stream));
         }
         return (int) WMH_OK;

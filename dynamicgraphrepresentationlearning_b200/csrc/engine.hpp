@@ -90,11 +90,12 @@ struct DeviceGraph
     u64 n = 0;                       // number_of_vertices()
     u64 m = 0;                       // number_of_edges() (directed entries)
     DeviceBuffer<RowDesc> desc;      // n
-    DeviceBuffer<u32> pool;          // neighbour pool, rows ascending & unique (+ aux tails, see `tail`)
+    DeviceBuffer<u32> pool;          // neighbour pool, rows ascending & unique (interleaved with aux words, see `tail`)
     u64 pool_used = 0;               // words of pool handed out (live + garbage)
     DeviceBuffer<u32> version;       // n: sampler-manager generation per vertex (graph/vertex.h:12)
     DeviceBuffer<u32> spare;         // second pool: compaction copies into it and swaps (no allocation in steady state)
-    u32 tail = 0;                    // 1: every row is followed by `degree` aux words (sampler cache | neighbour filter), MH node2vec
+    u32 tail = 0;                    // 1: neighbour i at begin + 2 i, its aux word (sampler cache | neighbour filter) at begin + 2 i + 1
+                                     //    (MH node2vec); 0: plain rows.  Doubles as the index shift of every row accessor.
 };
 
 // One prepared edge batch (sorted, deduplicated) and what the merge learned about it.
@@ -137,7 +138,8 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
                          PreparedBatch& out, u32* d_sorted_pairs_out /* nullable: count pairs, sorted (not deduped) */);
 // Applies the batch; returns the pool elements appended. Updates g.m, g.pool_used, version[], touched bitmap.
 void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch& b, bool is_delete, u32* d_touched_bitmap);
-void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity);
+// source_tail: layout (DeviceGraph::tail) of the rows being copied when it differs from g.tail (a layout switch); -1 = g.tail.
+void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int source_tail = -1);
 // Aux tails (MH node2vec): switch the layout on (one compaction), rebuild every tail (filter set, caches empty), or
 // only empty the sampler caches.
 void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g);
@@ -155,7 +157,8 @@ struct WalkParams
     const RowDesc* desc = nullptr;
     const u32* pool = nullptr;
     const u32* version = nullptr;
-    u32* pool_rw = nullptr;          // the same pool, writable: aux tails (MH node2vec; DeviceGraph::tail must be 1)
+    u32* pool_rw = nullptr;          // the same pool, writable: aux words (MH node2vec; DeviceGraph::tail must be 1)
+    u32 shift = 0;                   // DeviceGraph::tail: neighbour i of a row sits at pool[begin + (i << shift)]
     const u64* draw = nullptr;       // X[wpv][L]
     u32* walks = nullptr;            // [L][W_local] position-major
     u64 n = 0;                       // global vertices

@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(kBlock) coalesced_init_kernel(u32* __restrict_
 template <u32 R>
 __global__ void __launch_bounds__(kBlock) coalesced_advance_kernel(const RowDesc* __restrict__ desc, const u32* __restrict__ pool, const u32* __restrict__ cv,
                                                                    const u32* __restrict__ n_classes, SegDraws draws, u32 k, u32* __restrict__ rec,
-                                                                   u32* __restrict__ bitmap)
+                                                                   u32* __restrict__ bitmap, u32 shift)
 {
     const u32 nc = *n_classes;
     for (u32 c = blockIdx.x * kBlock + threadIdx.x; c < nc; c += gridDim.x * kBlock)
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(kBlock) coalesced_advance_kernel(const RowDesc
             if (j < k && u != kNoVertex)
             {
                 const RowDesc d = ld_desc(desc, u);
-                u = d.degree ? __ldg(pool + d.begin + mod_u64_u32(draws.x[j], d.degree)) : kNoVertex;
+                u = d.degree ? __ldg(pool + d.begin + ((u64) mod_u64_u32(draws.x[j], d.degree) << shift)) : kNoVertex;
             }
             t[j] = j < k ? u : kNoVertex;
         }
@@ -337,7 +337,7 @@ void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* c
                  bool merge)
 {
     const LaunchCtx& lc = s.lc;
-    coalesced_advance_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.wp.desc, s.wp.pool, cv, nc, draws, k, s.rec, merge ? s.bitmap : nullptr);
+    coalesced_advance_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.wp.desc, s.wp.pool, cv, nc, draws, k, s.rec, merge ? s.bitmap : nullptr, s.wp.shift);
     lc.count();
     if (merge)
     {
@@ -591,7 +591,7 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
     u64 draw_hash = 1469598103934665603ull;
     for (u64 i = 0; i < (u64) wp.wpv * wp.L; i++) draw_hash = (draw_hash ^ host_draw[i]) * 1099511628211ull;
     const CoalescedPlan::Key key{wp.desc, wp.pool, wp.walks, d_steps, wp.n, wp.w_local, draw_hash, wp.map.n_local, wp.wpv, wp.L, wp.map.rank, wp.map.world,
-                                 wp.map.whole * 65536u + wp.map.shared_first};
+                                 wp.map.whole * 65536u + wp.map.shared_first * 2u + wp.shift};
     if (!pl->exec || !(pl->key == key))
     {
         pl->drop_graph();

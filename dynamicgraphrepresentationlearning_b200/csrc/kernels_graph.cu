@@ -87,7 +87,7 @@ __global__ void sources_kernel(const u64* __restrict__ keys, u64* __restrict__ s
 // Per batch edge: rank of dst in the current row of src and whether it is already there.
 // change[i] = 1 when the edge changes the row (insert: absent, delete: present).
 __global__ void locate_kernel(const u64* __restrict__ keys, u64 k, const RowDesc* __restrict__ desc, const u32* __restrict__ pool,
-                              bool is_delete, u32* __restrict__ rank, u32* __restrict__ change)
+                              u32 rs, bool is_delete, u32* __restrict__ rank, u32* __restrict__ change)
 {
     const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
     if (i > k) return;
@@ -95,8 +95,8 @@ __global__ void locate_kernel(const u64* __restrict__ keys, u64 k, const RowDesc
     const u64 key = keys[i];
     const u32 src = (u32) (key >> 32), dst = (u32) key;
     const uint2 t = reinterpret_cast<const uint2*>(desc)[src];
-    const u32 r = lower_bound_u32(pool + t.x, t.y, dst);
-    const bool present = r < t.y && pool[t.x + r] == dst;
+    const u32 r = lower_bound_row(pool + t.x, t.y, dst, rs);
+    const bool present = r < t.y && pool[t.x + ((u64) r << rs)] == dst;
     rank[i] = r;
     change[i] = is_delete ? present : !present;
 }
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(256) merge_old_rows_kernel(const u32* __restri
                                                             const u64* __restrict__ keys, const u64* __restrict__ change_scan,
                                                             const u32* __restrict__ change, const u64* __restrict__ chunk_scan, u64 n_chunks,
                                                             const u64* __restrict__ alloc_scan, u64 pool_base,
-                                                            const RowDesc* __restrict__ desc, u32* __restrict__ pool, bool is_delete)
+                                                            const RowDesc* __restrict__ desc, u32* __restrict__ pool, u32 rs, bool is_delete)
 {
     const u64 chunk = ((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 lane = threadIdx.x & 31;
@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(256) merge_old_rows_kernel(const u32* __restri
     const u32 hi = min(d.y, (c + 1) * kChunk);
     for (u32 ia = c * kChunk + lane; ia < hi; ia += 32)
     {
-        const u32 a = pool[d.x + ia];
+        const u32 a = pool[d.x + ((u64) ia << rs)];
         // lower_bound of a among the slice's dsts
         u32 lo = 0, up = b_n;
         while (lo < up)
@@ -150,11 +150,11 @@ __global__ void __launch_bounds__(256) merge_old_rows_kernel(const u32* __restri
         if (is_delete)
         {
             if (lo < b_n && (u32) keys[b_lo + lo] == a && change[b_lo + lo]) continue;     // removed
-            out[ia - shift] = a;
+            out[(u64) (ia - shift) << rs] = a;
         }
         else
         {
-            out[ia + shift] = a;
+            out[(u64) (ia + shift) << rs] = a;
         }
     }
 }
@@ -162,13 +162,13 @@ __global__ void __launch_bounds__(256) merge_old_rows_kernel(const u32* __restri
 // Insert only: one thread per batch edge that is new to its row.
 __global__ void write_new_edges_kernel(const u64* __restrict__ keys, u64 k, const u64* __restrict__ slice, u64 n_sources,
                                        const u32* __restrict__ rank, const u32* __restrict__ change, const u64* __restrict__ change_scan,
-                                       const u64* __restrict__ alloc_scan, u64 pool_base, u32* __restrict__ pool)
+                                       const u64* __restrict__ alloc_scan, u64 pool_base, u32* __restrict__ pool, u32 rs)
 {
     const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= k || !change[i]) return;
     const u32 j = upper_segment_u64(slice, (u32) n_sources + 1, i);
     const u64 within = change_scan[i] - change_scan[slice[j]];
-    pool[pool_base + alloc_scan[j] + rank[i] + within] = (u32) keys[i];
+    pool[pool_base + alloc_scan[j] + ((rank[i] + within) << rs)] = (u32) keys[i];
 }
 
 // Repoint the rows, bump the sampler-manager generation (wharfmh.h:504 -> :539) and mark the touched bitmap.
@@ -184,23 +184,27 @@ __global__ void commit_rows_kernel(const u32* __restrict__ sources, u64 n_source
     if (bitmap) atomicOr(bitmap + (v >> 5), 1u << (v & 31));
 }
 
-// ---- aux tails (MH node2vec) ----------------------------------------------------------------------------
-// With g.tail a row of degree d owns 2 d pool words: d ascending neighbours, then d aux words.  Aux word i:
-//   low 16 bits   sampler cache of the state (cur = neighbour i, prev = this row's vertex)   (kernels_walk.cu)
-//   high 16 bits  block i of the row's neighbour filter                                        (common.cuh)
-// so everything a walker in state (cur, prev) needs from prev - cache word, filter block, the row itself - sits in
-// one short run of memory, next to the words its previous step already touched.
+// ---- aux words (MH node2vec) ----------------------------------------------------------------------------
+// With g.tail a row of degree d owns 2 d pool words, neighbours INTERLEAVED with their aux words:
+//     pool[begin + 2 i]      neighbour i (ascending)
+//     pool[begin + 2 i + 1]  aux word i:  low 16 bits   sampler cache of the state (cur = neighbour i, prev = this row's
+//                                                       vertex)                                      (kernels_walk.cu)
+//                                         high 16 bits  block i of the row's neighbour filter           (common.cuh)
+// A walker that picks neighbour i of its vertex as the next vertex loads both words with one 8-byte load: the second
+// is the sampler cache of the state it is about to enter, so the cache costs no memory access of its own (it used to
+// be a separate sector, and on graphs beyond the L2 a separate DRAM fetch, per step).  Rows without aux words
+// (g.tail == 0: deterministic engines) keep plain arrays; every row accessor takes the shift.
 
-// One warp per row: zero the tail, then set the filter bits of every neighbour.
+// One warp per row: zero the aux words, then set the filter bits of every neighbour.
 __device__ __forceinline__ void aux_build_row(u32* __restrict__ pool, u32 begin, u32 degree, u32 lane)
 {
-    u32* tail = pool + begin + degree;
-    for (u32 i = lane; i < degree; i += 32) tail[i] = 0;
+    u32* row = pool + begin;
+    for (u32 i = lane; i < degree; i += 32) row[2 * (u64) i + 1] = 0;
     __syncwarp();
     for (u32 i = lane; i < degree; i += 32)
     {
-        const u32 h = filter_hash(pool[begin + i]);
-        atomicOr(tail + filter_block(h, degree), filter_bits(h) << 16);
+        const u32 h = filter_hash(row[2 * (u64) i]);
+        atomicOr(row + 2 * (u64) filter_block(h, degree) + 1, filter_bits(h) << 16);
     }
 }
 
@@ -222,7 +226,7 @@ __global__ void __launch_bounds__(256) aux_build_sources_kernel(const u32* __res
 }
 
 // The cache half of aux word i of row p is a function of the rows of cur = neighbour i and of p and of version[cur].
-// Rows re-written by a batch get a fresh (empty) tail; this pass empties every other cache whose cur is a batch
+// Rows re-written by a batch get fresh (empty) aux words; this pass empties every other cache whose cur is a batch
 // source (bit set in the touched bitmap).  One warp per row over all rows: no reverse adjacency needed, so it is
 // exact for directed graphs.  bitmap == nullptr empties every cache (a fresh corpus, wharfmh.h:41,83,90).
 __global__ void __launch_bounds__(256) aux_invalidate_kernel(const RowDesc* __restrict__ desc, u64 n, u32* __restrict__ pool, const u32* __restrict__ bitmap)
@@ -230,16 +234,16 @@ __global__ void __launch_bounds__(256) aux_invalidate_kernel(const RowDesc* __re
     const u64 v = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
     if (v >= n) return;
     const uint2 d = reinterpret_cast<const uint2*>(desc)[v];
-    unsigned short* cache = reinterpret_cast<unsigned short*>(pool + d.x + d.y);      // low half of aux word i = cache[2 i]
+    unsigned short* halves = reinterpret_cast<unsigned short*>(pool + d.x);           // low half of aux word i = halves[4 i + 2]
     for (u32 i = threadIdx.x & 31; i < d.y; i += 32)
     {
         bool clear = true;
         if (bitmap)
         {
-            const u32 c = pool[d.x + i];
+            const u32 c = pool[d.x + 2 * (u64) i];
             clear = (__ldg(bitmap + (c >> 5)) >> (c & 31)) & 1u;
         }
-        if (clear) cache[2 * i] = 0;
+        if (clear) halves[4 * (u64) i + 2] = 0;
     }
 }
 
@@ -253,7 +257,7 @@ __global__ void degrees_kernel(const RowDesc* __restrict__ desc, u64 n, u32 row_
 
 // 8 lanes per row; rows above kBigRow are left to copy_big_rows_kernel.
 __global__ void __launch_bounds__(256) copy_rows_kernel(const RowDesc* __restrict__ desc, u64 n, const u32* __restrict__ pool,
-                                                       const u64* __restrict__ dst_offset, u32* __restrict__ dst)
+                                                       const u64* __restrict__ dst_offset, u32* __restrict__ dst, u32 ss, u32 ds)
 {
     const u64 g = ((u64) blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const u32 sub = threadIdx.x & 7;
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(const RowDesc* __restric
     const uint2 d = reinterpret_cast<const uint2*>(desc)[g];
     if (d.y > kBigRow) return;
     const u64 o = dst_offset[g];
-    for (u32 i = sub; i < d.y; i += 8) dst[o + i] = pool[d.x + i];
+    for (u32 i = sub; i < d.y; i += 8) dst[o + ((u64) i << ds)] = pool[d.x + ((u64) i << ss)];
 }
 
 struct IsBigRow
@@ -272,12 +276,12 @@ struct IsBigRow
 
 __global__ void __launch_bounds__(256) copy_big_rows_kernel(const u32* __restrict__ rows, const RowDesc* __restrict__ desc,
                                                            const u32* __restrict__ pool, const u64* __restrict__ dst_offset,
-                                                           u32* __restrict__ dst)
+                                                           u32* __restrict__ dst, u32 ss, u32 ds)
 {
     const u32 v = rows[blockIdx.x];
     const uint2 d = reinterpret_cast<const uint2*>(desc)[v];
     const u64 o = dst_offset[v];
-    for (u32 i = threadIdx.x; i < d.y; i += 256) dst[o + i] = pool[d.x + i];
+    for (u32 i = threadIdx.x; i < d.y; i += 256) dst[o + ((u64) i << ds)] = pool[d.x + ((u64) i << ss)];
 }
 
 __global__ void repoint_kernel(RowDesc* __restrict__ desc, u64 n, const u64* __restrict__ new_begin)
@@ -286,10 +290,11 @@ __global__ void repoint_kernel(RowDesc* __restrict__ desc, u64 n, const u64* __r
     if (v < n) desc[v].begin = (u32) new_begin[v];
 }
 
-void copy_all_rows(const LaunchCtx& lc, const RowDesc* desc, u64 n, const u32* pool, const u64* d_dst_offset, u32* d_dst)
+// Copies the neighbours of every row: element i from pool[begin + (i << ss)] to dst[offset + (i << ds)].
+void copy_all_rows(const LaunchCtx& lc, const RowDesc* desc, u64 n, const u32* pool, const u64* d_dst_offset, u32* d_dst, u32 ss, u32 ds)
 {
     if (n == 0) return;
-    copy_rows_kernel<<<div_up(n * 8, 256), 256, 0, lc.stream>>>(desc, n, pool, d_dst_offset, d_dst);
+    copy_rows_kernel<<<div_up(n * 8, 256), 256, 0, lc.stream>>>(desc, n, pool, d_dst_offset, d_dst, ss, ds);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
     Scratch<u32> big(lc.stream, n);
@@ -306,7 +311,7 @@ void copy_all_rows(const LaunchCtx& lc, const RowDesc* desc, u64 n, const u32* p
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
     if (n_big)
     {
-        copy_big_rows_kernel<<<(unsigned) n_big, 256, 0, lc.stream>>>(big.ptr, desc, pool, d_dst_offset, d_dst);
+        copy_big_rows_kernel<<<(unsigned) n_big, 256, 0, lc.stream>>>(big.ptr, desc, pool, d_dst_offset, d_dst, ss, ds);
         lc.count();
         WHARF_CUDA(cudaGetLastError());
     }
@@ -486,8 +491,9 @@ void graph_prepare_batch(const LaunchCtx& lc, const u32* d_pairs, u64 count, boo
 // swaps the two: garbage left by earlier batches is reclaimed, and a layout change (tail 0 -> 1) is the same copy.
 // The spare is kept, so steady-state compaction allocates nothing.  Aux tails come out rebuilt: filter set,
 // caches empty (the cache holds pure functions of (graph, key): dropping it is always safe).
-void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity)
+void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int source_tail)
 {
+    const u32 src_shift = source_tail < 0 ? g.tail : (u32) source_tail;      // layout of the rows being copied
     const u64 row_words = 1 + g.tail;
     const u64 live = g.m * row_words;
     u64 capacity = live + extra_capacity;
@@ -506,7 +512,7 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity)
     const u64 need = live + extra_capacity;
     if (g.spare.count < need + need / 8) g.spare.allocate(capacity);
     tr.mark("compact: spare pool");
-    copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, begin.ptr, g.spare.ptr);
+    copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, begin.ptr, g.spare.ptr, src_shift, g.tail);
     tr.mark("compact: copy_all_rows");
     repoint_kernel<<<div_up(g.n, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, begin.ptr);
     lc.count();
@@ -538,7 +544,7 @@ void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g)
 {
     if (g.tail) return;
     g.tail = 1;
-    graph_compact(lc, g, 0);
+    graph_compact(lc, g, 0, 0);                               // plain rows in, interleaved rows out
     // the pool the rows just left is too small to be the next compaction's target: size the spare now, while the
     // caller is still setting up a corpus, instead of inside an edge batch
     if (g.spare.count < g.pool.count) g.spare.allocate(g.pool.count);
@@ -551,7 +557,7 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     Trace tr(lc.stream);
     Scratch<u32> rank(lc.stream, k), change(lc.stream, k + 1);
     Scratch<u64> change_scan(lc.stream, k + 1);
-    locate_kernel<<<div_up(k + 1, 256), 256, 0, lc.stream>>>(b.keys.ptr, k, g.desc.ptr, g.pool.ptr, is_delete, rank.ptr, change.ptr);
+    locate_kernel<<<div_up(k + 1, 256), 256, 0, lc.stream>>>(b.keys.ptr, k, g.desc.ptr, g.pool.ptr, g.tail, is_delete, rank.ptr, change.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
     exclusive_sum(lc, change.ptr, change_scan.ptr, k + 1);
@@ -581,13 +587,13 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     {
         merge_old_rows_kernel<<<div_up(n_chunks * 32, 256), 256, 0, lc.stream>>>(b.sources.ptr, b.slice.ptr, ns, b.keys.ptr, change_scan.ptr,
                                                                                 change.ptr, chunk_scan.ptr, n_chunks, alloc_scan.ptr, base,
-                                                                                g.desc.ptr, g.pool.ptr, is_delete);
+                                                                                g.desc.ptr, g.pool.ptr, g.tail, is_delete);
         lc.count();
     }
     if (!is_delete)
     {
         write_new_edges_kernel<<<div_up(k, 256), 256, 0, lc.stream>>>(b.keys.ptr, k, b.slice.ptr, ns, rank.ptr, change.ptr, change_scan.ptr,
-                                                                      alloc_scan.ptr, base, g.pool.ptr);
+                                                                      alloc_scan.ptr, base, g.pool.ptr, g.tail);
         lc.count();
     }
     commit_rows_kernel<<<div_up(ns, 256), 256, 0, lc.stream>>>(b.sources.ptr, ns, new_degree.ptr, alloc_scan.ptr, base, g.desc.ptr,
@@ -614,7 +620,7 @@ void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr, u3
     degrees_kernel<<<div_up(g.n + 1, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, 1u, deg.ptr);
     lc.count();
     exclusive_sum(lc, deg.ptr, d_row_ptr, g.n + 1);
-    if (d_col) copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, d_row_ptr, d_col);
+    if (d_col) copy_all_rows(lc, g.desc.ptr, g.n, g.pool.ptr, d_row_ptr, d_col, g.tail, 0);
     WHARF_CUDA(cudaGetLastError());
 }
 

@@ -30,7 +30,7 @@ struct DevWalkParams
     const RowDesc* __restrict__ desc;
     const u32* __restrict__ pool;
     const u32* __restrict__ version;
-    u32* pool_rw;                     // the pool again, writable: aux tails behind the rows (MH node2vec)
+    u32* pool_rw;                     // the pool again, writable: aux words interleaved with the neighbours (MH node2vec)
     const u64* __restrict__ draw;
     u32* walks;
     u64 n;
@@ -38,6 +38,7 @@ struct DevWalkParams
     u64 first;                        // first local walk of this launch (bulk generation in chunks)
     ShardMap map;                     // local walk -> (replica, start vertex)
     u32 L;
+    u32 shift;                        // neighbour i of a row sits at pool[begin + (i << shift)] (1: interleaved with aux words)
     u32 init_strategy;
     float inv_p, inv_q;
     u64 seed;
@@ -48,6 +49,26 @@ __device__ __forceinline__ RowDesc load_desc(const RowDesc* __restrict__ desc, u
     const uint2 t = __ldg(reinterpret_cast<const uint2*>(desc) + v);
     return RowDesc{t.x, t.y};
 }
+
+// Neighbour i and its aux word in one 8-byte load.  The cache half of the aux word may be written by another walker
+// while this kernel runs; a stale copy only means the value is computed again (it is a memo of a pure function), so the
+// load may be served by L1 (WHARF_PAIR_LOAD: 0 = L2 only).
+template <int kMode>
+__device__ __forceinline__ uint2 load_pair_as(const u32* __restrict__ pool, RowDesc d, u32 i)
+{
+    const uint2* ptr = reinterpret_cast<const uint2*>(pool + d.begin + 2 * (u64) i);
+    if constexpr (kMode == 0) return __ldcg(ptr);
+    else if constexpr (kMode == 1) return *ptr;
+    else return __ldg(ptr);
+}
+
+// Neighbour i of a row; with aux words (shift 1, MH node2vec) the aux word of neighbour i follows it.
+__device__ __forceinline__ const u32* nbr_ptr(const DevWalkParams& p, RowDesc d, u32 i) { return p.pool + d.begin + ((u64) i << p.shift); }
+__device__ __forceinline__ u32* aux_ptr(const DevWalkParams& p, RowDesc d, u32 i) { return p.pool_rw + d.begin + 2 * (u64) i + 1; }
+#ifndef WHARF_PAIR_LOAD
+#define WHARF_PAIR_LOAD 0
+#endif
+__device__ __forceinline__ uint2 load_pair(const DevWalkParams& p, RowDesc d, u32 i) { return load_pair_as<WHARF_PAIR_LOAD>(p.pool, d, i); }
 
 // ---- deterministic rule (graph/wharfmh.h:304-309, :836-838) ----------------------------------------
 // next = N(cur)[ X[walk_id / n][pos - start_pos] % deg(cur) ]
@@ -93,7 +114,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deterministic_kernel(DevWalkP
             const RowDesc d = load_desc(p.desc, cur);
             if (d.degree == 0) { stopped = true; break; }            // isolated start (:277-286) or sink
             const u32 j = mod_u64_u32(__ldg(X + (pos - first)), d.degree);
-            cur = __ldg(p.pool + d.begin + j);
+            cur = __ldg(nbr_ptr(p, d, j));
             *out = cur;
         }
         if (!stopped) stopped = load_desc(p.desc, cur).degree == 0;  // last cell: only the degree matters
@@ -145,7 +166,7 @@ __global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkP
             if (d[k].degree)
             {
                 const u32 j = mod_u64_u32(__ldg(p.draw + rep_off[k] + pos), d[k].degree);
-                nxt[k] = __ldg(p.pool + d[k].begin + j);
+                nxt[k] = __ldg(nbr_ptr(p, d[k], j));
             }
         }
 #pragma unroll
@@ -176,7 +197,7 @@ __global__ void __launch_bounds__(kBlock) walk_deterministic_ilp_kernel(DevWalkP
 // (metropolis_hastings_sampler.h:69-108), a pure function of (seed, cur, prev, version[cur]) and the rows of cur
 // and prev.  A walker in state (cur, prev) has just traversed the edge prev -> cur, whose slot in the row of
 // prev it knows (it picked it), so the cache of the state is the low half of aux word `slot` of the row of prev
-// (aux tails: kernels_graph.cu):
+// (aux words: kernels_graph.cu):
 //     bit  15      valid
 //     bits 13..14  weight class of the init value with respect to prev (node2vec.h:74-88)
 //     bit  12      0: bits 0..11 = slot of the init value in the row of cur (rows up to 4096 neighbours)
@@ -203,7 +224,7 @@ __device__ __forceinline__ float class_weight(const DevWalkParams& p, u32 cls)
 
 // Index of the last element <= key of an ascending row (0 when there is none); branch-free halving, one load per
 // level.  *hit = whether that element equals key (std::binary_search of node2vec.h:112-119).
-__device__ __forceinline__ u32 row_find(const u32* __restrict__ row, u32 n, u32 key, bool* hit)
+__device__ __forceinline__ u32 row_find(const u32* __restrict__ row, u32 n, u32 key, bool* hit, u32 shift)
 {
     u32 base = 0;
     *hit = false;
@@ -211,10 +232,10 @@ __device__ __forceinline__ u32 row_find(const u32* __restrict__ row, u32 n, u32 
     while (n > 1)
     {
         const u32 half = n >> 1;
-        if (__ldg(row + base + half) <= key) base += half;
+        if (__ldg(row + ((u64) (base + half) << shift)) <= key) base += half;
         n -= half;
     }
-    *hit = __ldg(row + base) == key;
+    *hit = __ldg(row + ((u64) base << shift)) == key;
     return base;
 }
 
@@ -225,9 +246,9 @@ __device__ __forceinline__ u32 n2v_class(const DevWalkParams& p, u32 prev, RowDe
     if (dprev.degree == 0) return kClassFar;
     const u32 h = filter_hash(x);
     const u32 need = filter_bits(h);
-    if (((__ldcg(p.pool_rw + dprev.begin + dprev.degree + filter_block(h, dprev.degree)) >> 16) & need) != need) return kClassFar;   // proven absent
+    if (((__ldcg(aux_ptr(p, dprev, filter_block(h, dprev.degree))) >> 16) & need) != need) return kClassFar;   // proven absent
     bool hit;
-    row_find(p.pool + dprev.begin, dprev.degree, x, &hit);
+    row_find(p.pool + dprev.begin, dprev.degree, x, &hit, p.shift);
     return hit ? kClassNeighbour : kClassFar;
 }
 
@@ -245,16 +266,15 @@ __device__ InitValue n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dc
     const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
     u64 i = 0;
     u32 draw = 0;
-    const u32* __restrict__ nb = p.pool + dcur.begin;
     u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);                 // RANDOM :72-75
-    u32 cls = n2v_class(p, prev, dprev, __ldg(nb + slot));
+    u32 cls = n2v_class(p, prev, dprev, __ldg(nbr_ptr(p, dcur, slot)));
     if (p.init_strategy == WMH_INIT_BURNIN)                                                                // :77-85
     {
         for (int it = 0; it < 100; it++)
         {
             const u32 cdraw = (u32) i;
             const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);
-            const u32 ccls = n2v_class(p, prev, dprev, __ldg(nb + cslot));
+            const u32 ccls = n2v_class(p, prev, dprev, __ldg(nbr_ptr(p, dcur, cslot)));
             const float wn = class_weight(p, ccls), wo = class_weight(p, cls);
             bool acc = wo < wn;
             if (!acc) acc = unit_double(keyed_draw(p.seed, kDomSampler, cur, key_b, i++)) <= (double) wn / (double) wo;
@@ -276,17 +296,16 @@ __device__ __forceinline__ InitValue n2v_init_weight_group(const DevWalkParams& 
     if (has)
     {
         const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
-        const u32* aux = p.pool_rw + dprev.begin + dprev.degree;
         u32 slot[3], x[3], fh[3], fw[3];
 #pragma unroll
         for (u32 k = 0; k < 3; k++) slot[k] = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, sub + 8 * k), dcur.degree);
 #pragma unroll
-        for (u32 k = 0; k < 3; k++) x[k] = __ldg(p.pool + dcur.begin + slot[k]);
+        for (u32 k = 0; k < 3; k++) x[k] = __ldg(nbr_ptr(p, dcur, slot[k]));
 #pragma unroll
         for (u32 k = 0; k < 3; k++)
         {
             fh[k] = filter_hash(x[k]);
-            fw[k] = dprev.degree ? __ldcg(aux + filter_block(fh[k], dprev.degree)) >> 16 : 0u;
+            fw[k] = dprev.degree ? __ldcg(aux_ptr(p, dprev, filter_block(fh[k], dprev.degree))) >> 16 : 0u;
         }
         // classes: return / far are decided by the filter alone; the few proposals the filter cannot rule out (common
         // neighbours and 2.5 % false positives) are searched afterwards, one per lane and trip - the search is a
@@ -306,7 +325,7 @@ __device__ __forceinline__ InitValue n2v_init_weight_group(const DevWalkParams& 
             pending &= pending - 1u;
             const u32 xk = k == 0 ? x[0] : (k == 1 ? x[1] : x[2]);
             bool hit;
-            row_find(p.pool + dprev.begin, dprev.degree, xk, &hit);
+            row_find(p.pool + dprev.begin, dprev.degree, xk, &hit, p.shift);
             if (hit) { if (k == 0) cls0 = kClassNeighbour; else if (k == 1) cls1 = kClassNeighbour; else cls2 = kClassNeighbour; }
         }
 #pragma unroll
@@ -369,28 +388,32 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
         d = load_desc(p.desc, cur);
         prev = cur;
         if (pos > 0) prev = p.walks[(u64) (pos - 1) * p.w_local + w];                                  // wharfmh.h:819-823
-        else if (d.degree) prev = __ldg(p.pool + d.begin + mod_u64_u32(keyed_draw(p.seed, kDomState, walk_id, 0, 0), d.degree));   // node2vec.h:42-49
+        else if (d.degree) prev = __ldg(nbr_ptr(p, d, mod_u64_u32(keyed_draw(p.seed, kDomState, walk_id, 0, 0), d.degree)));   // node2vec.h:42-49
         dprev = load_desc(p.desc, prev);
         bool hit;
-        const u32 i = row_find(p.pool + dprev.begin, dprev.degree, cur, &hit);   // absent in a directed graph or after a delete
+        const u32 i = row_find(p.pool + dprev.begin, dprev.degree, cur, &hit, p.shift);   // absent in a directed graph or after a delete
         if (hit) slot = i;
     }
     const u32 first = pos;
     u32* out = p.walks + (u64) (pos + 1) * p.w_local + w;
     const u32 trips = warp_max_u32(owner ? last_pos - pos : 0u);
-    bool stopped = false;
+    bool stopped = false, have_carried = false;
+    u32 carried = 0;                                       // aux word that came with the load of cur
     for (u32 k = 0; k < trips; k++)
     {
         bool step = owner && !stopped && pos < last_pos;
         if (step && d.degree == 0) { stopped = true; step = false; }              // isolated start (:277-286) or sink
-        u32 cand = 0, cslot = 0, cache = 0, cls_new = kClassFar, last_slot = kNoSlot;
+        u32 cand = 0, cslot = 0, cache = 0, cls_new = kClassFar, last_slot = kNoSlot, cand_aux = 0;
         RowDesc dcand{0, 0};
-        u32* aux = p.pool_rw + dprev.begin + dprev.degree;                        // aux tail of the row of prev
         if (step)
         {
-            if (slot != kNoSlot) cache = __ldcg(aux + slot) & 0xFFFFu;
+            // cache of the state (cur, prev): the aux word next to cur in the row of prev - it came with the 8-byte load
+            // that picked cur one step ago; only a walker's first step (or a re-walk's) has to fetch it
+            if (slot != kNoSlot) cache = (have_carried ? carried : __ldcg(aux_ptr(p, dprev, slot))) & 0xFFFFu;
             cslot = mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree);   // propose_vertex - node2vec.h:97-105
-            cand = __ldg(p.pool + d.begin + cslot);
+            const uint2 pair = load_pair(p, d, cslot);
+            cand = pair.x;
+            cand_aux = pair.y;
             dcand = load_desc(p.desc, cand);
             cls_new = n2v_class(p, prev, dprev, cand);
         }
@@ -423,7 +446,7 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
         {
             cache = cache_encode(iv, d.degree);
             last_slot = iv.slot;
-            if (slot != kNoSlot) __stcg(reinterpret_cast<unsigned short*>(aux + slot), (unsigned short) cache);   // low half only
+            if (slot != kNoSlot) __stcg(reinterpret_cast<unsigned short*>(aux_ptr(p, dprev, slot)), (unsigned short) cache);   // low half only
         }
         if (step)
         {
@@ -441,11 +464,15 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
                         last_slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, ((u64) prev << 32) | __ldg(p.version + cur), last_slot), d.degree);
                 }
                 cslot = last_slot;
-                next = __ldg(p.pool + d.begin + cslot);
+                const uint2 pair = load_pair(p, d, cslot);
+                next = pair.x;
+                cand_aux = pair.y;
                 dcand = load_desc(p.desc, next);
             }
             __stcs(out, next);
             prev = cur; dprev = d; cur = next; d = dcand; slot = cslot;
+            carried = cand_aux;
+            have_carried = true;
             ++pos;
             out += p.w_local;
         }
@@ -485,7 +512,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkPar
         RowDesc d = load_desc(p.desc, cur);
         for (; pos < last_pos && d.degree; ++pos, out += p.w_local)
         {
-            cur = __ldg(p.pool + d.begin + mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree));
+            cur = __ldg(nbr_ptr(p, d, mod_u64_u32(keyed_draw(p.seed, kDomStep, walk_id, pos, 0), d.degree)));
             __stcs(out, cur);
             d = load_desc(p.desc, cur);
         }
@@ -501,7 +528,7 @@ __global__ void __launch_bounds__(kWalkBlock) walk_deepwalk_mh_kernel(DevWalkPar
 // each one once: states are numbered in row order (state e = eoff[prev] + slot of cur in the row of prev), rank g
 // owns the states of the vertex range [split[g], split[g + 1]) (equal edge counts), and its kernel stores the 16-bit
 // cache words straight into the exchange buffer of every peer (32-byte vector stores over NVLink: 16 consecutive
-// states) and into its own aux tails.  After the barrier every rank copies the words it received into its tails.
+// states) and into its own aux words.  After the barrier every rank copies the words it received into its own.
 
 struct DegreeOf
 {
@@ -574,7 +601,7 @@ __global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParam
                     dprev = load_desc(p.desc, v);
                 }
                 slot = (u32) (e - row_off);
-                cur = __ldg(p.pool + dprev.begin + slot);
+                cur = __ldg(nbr_ptr(p, dprev, slot));
                 d = load_desc(p.desc, cur);
             }
             const bool has = mine && d.degree != 0;                      // a walker on a sink never samples
@@ -589,7 +616,7 @@ __global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParam
             const u32 word = has ? cache_encode(iv, d.degree) : 0u;
             acc[r >> 1] |= word << ((r & 1) * 16);
             if (mine && sub == 0)
-                __stcg(reinterpret_cast<unsigned short*>(p.pool_rw + dprev.begin + dprev.degree + slot), (unsigned short) word);   // own tail, low half
+                __stcg(reinterpret_cast<unsigned short*>(aux_ptr(p, dprev, slot)), (unsigned short) word);   // own aux word, low half
         }
         if (remote)
         {
@@ -617,8 +644,8 @@ __global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __
     if (v >= n || (v >= split[rank] && v < split[rank + 1])) return;
     const RowDesc d = load_desc(desc, v);
     const unsigned short* src = received + __ldg(eoff + v);
-    unsigned short* cache = reinterpret_cast<unsigned short*>(pool + d.begin + d.degree);      // low half of aux word i = cache[2 i]
-    for (u32 i = sub; i < d.degree; i += 8) cache[2 * i] = __ldcs(src + i);
+    unsigned short* halves = reinterpret_cast<unsigned short*>(pool + d.begin);                // low half of aux word i = halves[4 i + 2]
+    for (u32 i = sub; i < d.degree; i += 8) halves[4 * (u64) i + 2] = __ldcs(src + i);
 }
 
 // Flag barrier in peer memory: lane g tells rank g "rank `rank` reached epoch", then waits for rank g's word in the
@@ -758,6 +785,7 @@ DevWalkParams to_dev(const WalkParams& wp)
     p.desc = wp.desc; p.pool = wp.pool; p.version = wp.version; p.pool_rw = wp.pool_rw; p.draw = wp.draw; p.walks = wp.walks;
     p.n = wp.n; p.w_local = wp.w_local; p.map = wp.map; p.L = wp.L;
     p.init_strategy = wp.init_strategy;
+    p.shift = wp.shift;
     p.inv_p = 1 / wp.p;                                                 // node2vec.h:78
     p.inv_q = 1 / wp.q;                                                 // node2vec.h:86
     p.seed = wp.seed;

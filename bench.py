@@ -54,14 +54,17 @@ def log(*a):
 # clocks: sample nvidia-smi during the timed region
 # ----------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """SM clock and throttle reasons DURING the timed region: NVML polled every 5 ms from a thread (the timed region of the
-    default run is ~150 ms, one nvidia-smi process launch would not fit into it); nvidia-smi when NVML is unavailable."""
+    """SM clock and throttle reasons DURING the timed region: NVML polled every 20 ms from a thread of RANK 0 only (the
+    timed region of the default run is ~150 ms, one nvidia-smi process launch would not fit into it); nvidia-smi when
+    NVML is unavailable.  Other ranks do not poll: NVML queries take driver-wide locks, and eight processes polling
+    every few milliseconds showed up as ~1 ms of launch gaps inside a 4 ms multi-launch pass at N = 8."""
     FIELDS = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, enabled: bool = True):
         self.gpu = gpu_index
+        self.enabled = enabled
         self.sm: list[int] = []
         self.max_sm = None
         self.reasons: set[str] = set()
@@ -69,6 +72,9 @@ class ClockSampler:
         self._stop = threading.Event()
         self._thread = None
         self._nvml = None
+        if not enabled:
+            self.source = "not sampled on this rank"
+            return
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -91,7 +97,7 @@ class ClockSampler:
                 self.reasons.update(name for mask, name in masks if bits & mask)
             except Exception:
                 pass
-            self._stop.wait(0.005)
+            self._stop.wait(0.02)
 
     def _poll_smi(self):
         while not self._stop.is_set():
@@ -110,13 +116,15 @@ class ClockSampler:
             self._stop.wait(0.2)
 
     def __enter__(self):
-        self._thread = threading.Thread(target=self._poll_nvml if self._nvml else self._poll_smi, daemon=True)
-        self._thread.start()
+        if self.enabled:
+            self._thread = threading.Thread(target=self._poll_nvml if self._nvml else self._poll_smi, daemon=True)
+            self._thread.start()
         return self
 
     def __exit__(self, *exc):
         self._stop.set()
-        self._thread.join(timeout=6)
+        if self._thread:
+            self._thread.join(timeout=6)
 
     def summary(self) -> dict:
         return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.max_sm, "reasons": sorted(self.reasons),
@@ -306,7 +314,7 @@ def main():
         one_step()
     launches0 = engine.kernel_launches()
     barrier()
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank, enabled=rank == 0) as clocks:
         wall0 = time.perf_counter()
         kernel_ms, local_steps = [], 0
         for _ in range(args.steps):

@@ -15,6 +15,7 @@
 
 #include "wharfmh_b200.h"
 
+#include <array>
 #include <chrono>
 #include <cstdint>
 #include <cstdlib>
@@ -107,6 +108,8 @@ namespace config   // config/globals.h:7-29
     inline int device                 = 0;
     inline int search_mode            = WMH_SEARCH_AUTO;
     inline int generate_mode          = WMH_GENERATE_AUTO;      // schedule of deterministic bulk generation (same corpus)
+    inline uint32_t rank              = 0;                      // one process per GPU: this process's share of the corpus
+    inline uint32_t world             = 1;                      // (whole replicas first, the rest by start vertex; wharfmh_b200.h)
 }
 
 namespace dynamic_graph_representation_learning_with_metropolis_hastings
@@ -131,6 +134,8 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
             c.generate_mode = static_cast<uint32_t>(config::generate_mode);
             c.seed = config::random_seed;
             c.device = config::device;
+            c.rank = config::rank;
+            c.world = config::world;
             return c;
         }
     }
@@ -255,6 +260,32 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
         void print_memory_pool_stats() const { memory_footprint(); }                                    // :1003
 
         wmh_engine* handle() const { return engine_; }
+
+        // -- several processes, one GPU each (no counterpart in the single-process reference) ----------------------
+        // Global ids of the walks this process owns, ascending; the rank that owns a walk.
+        std::vector<types::WalkID> local_walk_ids() const
+        {
+            std::vector<types::WalkID> ids(wmh_local_walk_ids(engine_, nullptr, 0));
+            if (!ids.empty()) wmh_local_walk_ids(engine_, ids.data(), ids.size());
+            return ids;
+        }
+        uint32_t walk_owner(types::WalkID walk_id) const { return wmh_walk_owner(engine_, walk_id); }
+        // Peer memory between the processes of one box (wharfmh_b200.h, wmh_peer_*): create the exchange window, hand the
+        // returned handle to every other process (MPI_Allgather, a file ...), then attach all of them in rank order.
+        std::array<unsigned char, WMH_PEER_HANDLE_BYTES> peer_create(uint64_t bytes = 0)
+        {
+            std::array<unsigned char, WMH_PEER_HANDLE_BYTES> handle{};
+            if (bytes == 0) bytes = wmh_peer_bytes_needed(engine_) * 5 / 4 + (1u << 20);
+            detail::check(wmh_peer_create(engine_, bytes, handle.data()));
+            return handle;
+        }
+        void peer_attach(const std::vector<std::array<unsigned char, WMH_PEER_HANDLE_BYTES>>& handles)
+        {
+            std::vector<unsigned char> blob;
+            for (const auto& h : handles) blob.insert(blob.end(), h.begin(), h.end());
+            detail::check(wmh_peer_attach(engine_, blob.data()));
+        }
+        void peer_detach() { detail::check(wmh_peer_detach(engine_)); }
 
     private:
         wmh_engine* engine_ = nullptr;

@@ -307,6 +307,9 @@ def main():
     def one_step():
         flush.fill_(1)                                                   # L2 flush between timed iterations
         torch.cuda.synchronize()
+        if peers:
+            barrier()                                                    # ranks enter the pass together: the peer exchange meets at a flag
+                                                                         # barrier ON the device, so host-side skew would be timed as waiting
         steps = engine.generate_initial_random_walks()                   # device-timed inside (CUDA events on the engine stream)
         return steps, engine.last_walk_kernel_ms()
 

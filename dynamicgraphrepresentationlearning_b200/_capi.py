@@ -93,6 +93,8 @@ SIGNATURES = {
     "wmh_global_to_local_walk": (C.c_int64, [vp, u64]),
     "wmh_walk_owner": (u32, [vp, u64]),
     "wmh_local_walk_ids": (u64, [vp, vp, u64]),
+    "wmh_partition_owner": (u32, [u64, u32, u32, u64]),
+    "wmh_partition_local_walk_ids": (u64, [u64, u32, u32, u32, vp, u64]),
     "wmh_corpus_fingerprint": (i32, [vp, PU64]),
     "wmh_build_index": (i32, [vp]),
     "wmh_index_find_next": (i32, [vp, u32, u64, u32, PU32, C.POINTER(i32)]),

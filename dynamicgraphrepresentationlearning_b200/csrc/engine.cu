@@ -968,6 +968,22 @@ uint32_t wmh_walk_owner(const wmh_engine* e, uint64_t walk_id)
     return (e->have_walks ? e->map : config_map(*e)).owner(walk_id);
 }
 
+uint32_t wmh_partition_owner(uint64_t n, uint32_t walks_per_vertex, uint32_t world, uint64_t walk_id)
+{
+    if (n == 0 || world == 0 || walks_per_vertex == 0) return 0;
+    return make_shard_map(n, walks_per_vertex, 0, world).owner(walk_id);
+}
+
+uint64_t wmh_partition_local_walk_ids(uint64_t n, uint32_t walks_per_vertex, uint32_t rank, uint32_t world, uint64_t* out, uint64_t capacity)
+{
+    if (n == 0 || world == 0 || rank >= world || walks_per_vertex == 0) return 0;
+    const ShardMap m = make_shard_map(n, walks_per_vertex, rank, world);
+    const u64 count = m.local_walks();
+    if (out)
+        for (u64 w = 0; w < count && w < capacity; w++) out[w] = m.global_id(w);
+    return count;
+}
+
 uint64_t wmh_local_walk_ids(const wmh_engine* e, uint64_t* out, uint64_t capacity)
 {
     if (!e) return 0;

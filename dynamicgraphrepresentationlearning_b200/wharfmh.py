@@ -339,6 +339,21 @@ def trim_memory(device: int = 0) -> None:
 
 # ---- pairings (walks/pairings.h) over torch / raw device pointers ------------------------------------
 
+def partition_owner(n: int, walks_per_vertex: int, world: int, walk_id: int) -> int:
+    """Rank that owns a global walk id under the sharding rule of include/wharfmh_b200.h (host arithmetic, no device)."""
+    return int(capi.load().wmh_partition_owner(int(n), int(walks_per_vertex), int(world), int(walk_id)))
+
+
+def partition_local_walk_ids(n: int, walks_per_vertex: int, rank: int, world: int) -> np.ndarray:
+    """Global ids of the walks `rank` of `world` owns, ascending (host arithmetic, no device)."""
+    lib = capi.load()
+    count = int(lib.wmh_partition_local_walk_ids(int(n), int(walks_per_vertex), int(rank), int(world), None, 0))
+    out = np.empty(count, dtype=np.uint64)
+    if count:
+        lib.wmh_partition_local_walk_ids(int(n), int(walks_per_vertex), int(rank), int(world), out.ctypes.data_as(C.c_void_p), count)
+    return out
+
+
 def szudzik_pair(x: int, y: int) -> int:
     return int(capi.load().wmh_szudzik_pair(x, y))
 

@@ -205,6 +205,11 @@ WMH_API int64_t  wmh_global_to_local_walk(const wmh_engine* e, uint64_t walk_id)
  * local walk order (ascending); returns their number. */
 WMH_API uint32_t wmh_walk_owner(const wmh_engine* e, uint64_t walk_id);
 WMH_API uint64_t wmh_local_walk_ids(const wmh_engine* e, uint64_t* out, uint64_t capacity);
+/* The same rule without an engine (pure host arithmetic, no device needed): a launcher can decide placement, and a
+ * consumer can route a walk id to its owner, from (n, walks_per_vertex, world) alone. */
+WMH_API uint32_t wmh_partition_owner(uint64_t n, uint32_t walks_per_vertex, uint32_t world, uint64_t walk_id);
+WMH_API uint64_t wmh_partition_local_walk_ids(uint64_t n, uint32_t walks_per_vertex, uint32_t rank, uint32_t world,
+                                              uint64_t* out, uint64_t capacity);
 /* FNV-1a-64 fingerprint of the local corpus in walk() text form (computed on the device). */
 WMH_API int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum_of_row_hashes);
 

@@ -61,6 +61,38 @@ def test_host_only_entry_points(wharf, golden):
         assert wharf.szudzik_unpair(wharf.szudzik_pair(int(x), int(y))) == (int(x), int(y))
 
 
+@pytest.mark.parametrize("n,world,wpv", [(512, 2, 2), (509, 3, 2), (1000, 8, 10), (7, 8, 3), (64, 5, 10), (300, 4, 10), (129, 2, 5),
+                                         (1 << 14, 8, 10), (1 << 14, 7, 10), (1000, 6, 9), (33, 1, 4), (10, 8, 1)])
+def test_partition_rule_on_the_host(wharf, n, world, wpv):
+    """The sharding rule (whole replicas first, the remaining replicas in gcd(world, rest) groups by rotated start-vertex
+    slots) is host arithmetic: every walk has exactly one owner, local order is ascending, shares are balanced, and
+    wmh_partition_owner agrees with the id lists.  (On a GPU tests/test_gpu_parity.py::test_shard_rule_is_a_partition
+    checks the engine against the same lists.)"""
+    import math
+    owner = np.full(n * wpv, -1, dtype=np.int64)
+    q = wpv // world if world > 1 else 0
+    rest = wpv - world * q if world > 1 else wpv
+    g = math.gcd(world, rest) if rest else world
+    counts = []
+    for r in range(world):
+        ids = wharf.partition_local_walk_ids(n, wpv, r, world).astype(np.int64)
+        assert ids.size == 0 or ((np.diff(ids) > 0).all() and ids.min() >= 0 and ids.max() < n * wpv)
+        assert (owner[ids] == -1).all()
+        owner[ids] = r
+        counts.append(ids.size)
+        if q:
+            assert np.array_equal(ids[: q * n], np.arange(r * q * n, (r + 1) * q * n))      # its whole replicas
+        for walk in ids[:: max(1, ids.size // 97)]:
+            assert wharf.partition_owner(n, wpv, world, int(walk)) == r
+    assert (owner >= 0).all()
+    shared_per_rank = (rest // g) * n // (world // g)
+    assert max(counts) - min(counts) <= max(1, rest // g) and abs(counts[0] - (q * n + shared_per_rank)) <= max(1, rest // g)
+    # a shared replica's start vertices rotate from block to block inside its group
+    if world == 8 and n >= 1000 and wpv == 10:
+        shared = owner[8 * n: 9 * n]
+        assert set(shared.tolist()) == {0, 1, 2, 3} and len({int(shared[b * 4]) for b in range(100)}) > 1
+
+
 def test_no_cpu_fallback(wharf):
     import torch
     if torch.cuda.is_available():

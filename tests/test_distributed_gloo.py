@@ -1,7 +1,7 @@
 """CPU tests (gloo, world_size 2) of the multi-rank host logic: batch broadcast (C1), variable-length all-gather
 of affected walk ids (C2) and the walk sharding rule.  The per-rank engine is a stand-in backed by the CPU
-oracle (tests may use the oracle; the product never does), sharded exactly like the CUDA engine:
-start % world == rank."""
+oracle (tests may use the oracle; the product never does), sharded exactly like the CUDA engine: the host-side
+partition rule of the library itself (wmh_partition_owner / wmh_partition_local_walk_ids)."""
 import os
 import sys
 from pathlib import Path
@@ -22,7 +22,7 @@ class OracleShard:
         self.cfg, self.n = cfg, n
 
     def _mine(self, ids):
-        return ids[(ids % self.n) % self.cfg.world == self.cfg.rank]
+        return ids[np.isin(ids, self.local_walk_ids())]
 
     def number_of_vertices(self):
         return self.n
@@ -47,11 +47,12 @@ class OracleShard:
         return self._update(edges, True, remove_dups, apply_walk_updates)
 
     def walk_owner(self, walk_id):
-        return int((walk_id % self.n) % self.cfg.world)
+        from dynamicgraphrepresentationlearning_b200 import partition_owner
+        return partition_owner(self.n, self.cfg.walks_per_vertex, self.cfg.world, walk_id)
 
     def local_walk_ids(self):
-        starts = np.arange(self.cfg.rank, self.n, self.cfg.world, dtype=np.uint64)
-        return (np.arange(self.cfg.walks_per_vertex, dtype=np.uint64)[:, None] * np.uint64(self.n) + starts[None, :]).reshape(-1)
+        from dynamicgraphrepresentationlearning_b200 import partition_local_walk_ids
+        return partition_local_walk_ids(self.n, self.cfg.walks_per_vertex, self.cfg.rank, self.cfg.world)
 
     def walks(self):
         return self.o.walks()[self.local_walk_ids().astype(np.int64)]
@@ -88,7 +89,7 @@ def _worker(rank, world, port, out_dir):
             ok &= sharded.number_of_edges() == single.m
             gids, rows = sharded.local_walks()
             ok &= np.array_equal(rows, single.walks()[gids.astype(np.int64)])
-            ok &= bool(((gids % n) % world == rank).all())
+            ok &= all(sharded.engine.walk_owner(int(g)) == rank for g in gids[::7])
         ok &= sharded.walk(5) == sharded.walk(5) and sharded.walk(258).startswith("2 ")
         empty = sharded.insert_edges_batch(np.empty((0, 2), dtype=np.uint32) if rank == 0 else None)
         ok &= empty.shape[0] == 0

@@ -95,6 +95,11 @@ SIGNATURES = {
     "wmh_local_walk_ids": (u64, [vp, vp, u64]),
     "wmh_partition_owner": (u32, [u64, u32, u32, u64]),
     "wmh_partition_local_walk_ids": (u64, [u64, u32, u32, u32, vp, u64]),
+    "wmh_parse_adjacency_graph": (i32, [vp, u64, PU64, PU64, vp, vp]),
+    "wmh_format_adjacency_graph": (u64, [u64, u64, vp, vp, vp, u64]),
+    "wmh_parse_edge_list": (i32, [vp, u64, vp, u64, PU64, PU64]),
+    "wmh_format_walks": (u64, [vp, u64, u32, vp, u64]),
+    "wmh_write_walks": (i32, [vp, vp, u64, cp, i32, PU64]),
     "wmh_corpus_fingerprint": (i32, [vp, PU64]),
     "wmh_build_index": (i32, [vp]),
     "wmh_index_find_next": (i32, [vp, u32, u64, u32, PU32, C.POINTER(i32)]),

@@ -49,6 +49,8 @@ int guarded(F&& f)
 }
 }  // namespace
 
+int wharf::report_failure(int code, const std::string& msg) { return fail(code, msg); }
+
 namespace
 {
 void peer_release(PeerLink& link)

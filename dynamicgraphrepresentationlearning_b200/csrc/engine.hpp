@@ -8,10 +8,14 @@
 #include <cstdio>
 #include <cstdlib>
 #include <functional>
+#include <string>
 #include <vector>
 
 namespace wharf
 {
+// Records the message wmh_last_error() returns on this thread and hands the status code back (engine.cu).
+int report_failure(int code, const std::string& msg);
+
 struct LaunchCtx
 {
     cudaStream_t stream = nullptr;

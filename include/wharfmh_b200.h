@@ -309,6 +309,34 @@ WMH_API int wmh_generate_batch_of_edges_device(int device, uint64_t edges_number
 WMH_API int wmh_pairs_to_csr_device(int device, uint64_t n, const uint32_t* d_pairs, uint64_t count,
                                     uint64_t* d_offsets, uint32_t* d_edges);
 
+/* ---- ingest and export: the text formats either side of the path (host code, no device needed) ---- */
+
+/* Ligra "AdjacencyGraph" text (libs/compressed_trees/common/IO.h:67-106, read_unweighted_graph): the tokens
+ * "AdjacencyGraph", n, m, n offsets, m neighbour ids.  Call with offsets = edges = NULL for *n and *m, then
+ * with offsets[n] (no n+1-th entry, as the reference) and edges[m].  The token count must be n + m + 3
+ * (IO.h:94 asserts it); offsets must be non-decreasing and <= m, neighbour ids < n. */
+WMH_API int wmh_parse_adjacency_graph(const char* text, uint64_t bytes, uint64_t* n, uint64_t* m,
+                                      uint64_t* offsets, uint32_t* edges);
+/* The same format written out (what experiments/bin/SNAPtoAdj produces).  Returns the bytes needed; writes
+ * only when capacity is enough (no terminating NUL). */
+WMH_API uint64_t wmh_format_adjacency_graph(uint64_t n, uint64_t m, const uint64_t* offsets, const uint32_t* edges,
+                                            char* out, uint64_t capacity);
+/* SNAP edge list ("u v" per line; blank lines and lines starting with '#' or '%' skipped): the input of
+ * SNAPtoAdj and of create_edge_stream (experiments/src/vertex-classification.cpp:5-38).  pairs receives
+ * (u, v) in file order; *count = pairs in the text (also when pairs is NULL: call twice), *vertices =
+ * largest id + 1.  WMH_ERR_RANGE when pairs is given but holds fewer than *count. */
+WMH_API int wmh_parse_edge_list(const char* text, uint64_t bytes, uint32_t* pairs, uint64_t capacity,
+                                uint64_t* count, uint64_t* vertices);
+/* Rows of walk_length vertices (WMH_NO_VERTEX padded, as wmh_walks_copy / wmh_walks_gather return them) as
+ * text: each walk as WharfMH::walk prints it (graph/wharfmh.h:365-394, every vertex followed by a space)
+ * and a newline.  Returns the bytes needed; writes only when capacity is enough. */
+WMH_API uint64_t wmh_format_walks(const uint32_t* rows, uint64_t count, uint32_t walk_length, char* out,
+                                  uint64_t capacity);
+/* walks.txt hand-off of the walks a batch changed (vertex-classification.cpp:167-178): gathers the named
+ * walks (global ids held by this engine) from the device and writes them with wmh_format_walks. */
+WMH_API int wmh_write_walks(wmh_engine* e, const uint64_t* walk_ids, uint64_t count, const char* path, int append,
+                            uint64_t* bytes_written);
+
 #ifdef __cplusplus
 }
 #endif

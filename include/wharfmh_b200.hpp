@@ -15,6 +15,7 @@
 
 #include "wharfmh_b200.h"
 
+#include <algorithm>
 #include <array>
 #include <chrono>
 #include <cstdint>
@@ -248,6 +249,15 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
                                                          size_t nn = std::numeric_limits<size_t>::max(), bool apply_walk_updates = true, bool run_seq = false)
         { return batch(true, m, edges, sorted, remove_dups, nn, apply_walk_updates, run_seq); }
 
+        // experiments/src/vertex-classification.cpp:167-178: walk(id) + newline for every id, gathered on the device in bulk
+        // and written to `path` (the walks.txt the downstream trainer reads).  Returns the bytes written.
+        size_t write_walks(const char* path, const pbbs::sequence<types::WalkID>& walk_ids, bool append = false)
+        {
+            uint64_t written = 0;
+            detail::check(wmh_write_walks(engine_, walk_ids.begin(), walk_ids.size(), path, append ? 1 : 0, &written));
+            return written;
+        }
+
         // :928 (device memory instead of allocator pools)
         void memory_footprint() const
         {
@@ -340,22 +350,59 @@ namespace utility   // utils/utility.h
                                                                                 double b = 0.2, double c = 0.1, bool /*run_seq*/ = false);
 }
 
+namespace detail
+{
+    inline std::string read_file(const char* fname)
+    {
+        std::ifstream in(fname, std::ios::in | std::ios::binary);
+        if (!in) throw std::runtime_error(std::string("Unable to open file: ") + fname);      // IO.h:54-57 aborts here
+        std::ostringstream all;
+        all << in.rdbuf();
+        return all.str();
+    }
+}
+
 // libs/compressed_trees/common/IO.h:67-106: Ligra "AdjacencyGraph" text format -> (n, m, offsets[n], edges[m])
 inline std::tuple<size_t, size_t, uintE*, uintV*> read_unweighted_graph(const char* fname, bool /*is_symmetric*/, bool /*mmap*/ = false)
 {
-    std::ifstream in(fname);
-    if (!in) throw std::runtime_error(std::string("cannot open ") + fname);
-    std::string header;
-    size_t n = 0, m = 0;
-    in >> header >> n >> m;
-    if (header != "AdjacencyGraph") throw std::runtime_error("not an AdjacencyGraph file");
+    const std::string text = detail::read_file(fname);
+    uint64_t n = 0, m = 0;
+    dygrl::detail::check(wmh_parse_adjacency_graph(text.data(), text.size(), &n, &m, nullptr, nullptr));
     std::cout << "Vertices: " << n << " Edges: " << m << std::endl;
     uintE* offsets = pbbs::new_array_no_init<uintE>(n);
     uintV* edges = pbbs::new_array_no_init<uintV>(m);
-    for (size_t i = 0; i < n; i++) in >> offsets[i];
-    for (size_t i = 0; i < m; i++) in >> edges[i];
-    if (!in) throw std::runtime_error("truncated AdjacencyGraph file");
+    const int rc = wmh_parse_adjacency_graph(text.data(), text.size(), &n, &m, offsets, edges);
+    if (rc != WMH_OK)
+    {
+        pbbs::free_array(offsets);
+        pbbs::free_array(edges);
+        dygrl::detail::check(rc);
+    }
     return {n, m, offsets, edges};
+}
+
+// experiments/src/vertex-classification.cpp:5-38: the lines "u v" of file -f in partitions of -eps lines, every line as
+// (u, v) and (v, u); each partition is a heap array the caller passes to insert_edges_batch(size, array, false, true).
+inline void create_edge_stream(const char* fname, size_t edge_partition_size, std::vector<std::pair<std::tuple<uintV, uintV>*, uintV>>& stream)
+{
+    if (edge_partition_size == 0) throw std::invalid_argument("edge partition size must be positive");
+    const std::string text = detail::read_file(fname);
+    uint64_t lines = 0, vertices = 0;
+    dygrl::detail::check(wmh_parse_edge_list(text.data(), text.size(), nullptr, 0, &lines, &vertices));
+    std::vector<uint32_t> pairs(2 * lines);
+    dygrl::detail::check(wmh_parse_edge_list(text.data(), text.size(), pairs.data(), lines, &lines, &vertices));
+    for (size_t first = 0; first < lines; first += edge_partition_size)
+    {
+        const size_t k = std::min<size_t>(edge_partition_size, lines - first);
+        auto* part = new std::tuple<uintV, uintV>[2 * k];
+        for (size_t j = 0; j < k; j++)
+        {
+            const uintV u = pairs[2 * (first + j)], v = pairs[2 * (first + j) + 1];
+            part[2 * j] = std::make_tuple(u, v);
+            part[2 * j + 1] = std::make_tuple(v, u);
+        }
+        stream.emplace_back(part, static_cast<uintV>(2 * k));
+    }
 }
 
 // libs/compressed_trees/pbbslib/parse_command_line.h:30-80
@@ -371,5 +418,12 @@ struct commandLine
     long getOptionLongValue(const std::string& option, long def) const { char* v = getOptionValue(option); return v ? std::atol(v) : def; }
     double getOptionDoubleValue(const std::string& option, double def) const { char* v = getOptionValue(option); return v ? std::atof(v) : def; }
 };
+
+// The reference's own signature (vertex-classification.cpp:5): file from -f (default "stream"), partition size from -eps (5000).
+inline void create_edge_stream(commandLine& command_line, std::vector<std::pair<std::tuple<uintV, uintV>*, uintV>>& stream)
+{
+    const std::string fname = command_line.getOptionValue("-f", "stream");
+    create_edge_stream(fname.c_str(), static_cast<size_t>(command_line.getOptionLongValue("-eps", 5000)), stream);
+}
 
 #endif  // WHARFMH_B200_HPP

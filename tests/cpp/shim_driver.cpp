@@ -5,9 +5,39 @@
 #include "wharfmh_b200.hpp"
 
 #include <cstdio>
+#include <fstream>
+#include <string>
 
-int main()
+// Host-only part (runs without a GPU): the text formats either side of the path.  argv[1] = scratch directory.
+static void text_formats(const std::string& dir)
 {
+    const std::string adj_path = dir + "/toy.adj", stream_path = dir + "/toy.stream";
+    { std::ofstream f(adj_path); f << "AdjacencyGraph\n3\n4\n0\n2\n3\n1\n2\n0\n0\n"; }
+    auto [gn, gm, goff, gadj] = read_unweighted_graph(adj_path.c_str(), true);               // IO.h:67
+    std::printf("adjacency n %zu m %zu offsets %llu %llu %llu edges %u %u %u %u\n", gn, gm, (unsigned long long) goff[0], (unsigned long long) goff[1],
+                (unsigned long long) goff[2], gadj[0], gadj[1], gadj[2], gadj[3]);
+    pbbs::free_array(goff);
+    pbbs::free_array(gadj);
+    { std::ofstream f(stream_path); f << "# five lines\n0 1\n1 2\n2 3\n3 4\n4 5\n"; }
+    char a0[] = "driver", a1[] = "-f", a3[] = "-eps", a4[] = "2";
+    std::string a2 = stream_path;
+    char* argv[] = {a0, a1, a2.data(), a3, a4};
+    commandLine cl(5, argv);
+    std::vector<std::pair<std::tuple<uintV, uintV>*, uintV>> stream;
+    create_edge_stream(cl, stream);                                                           // vertex-classification.cpp:5
+    std::printf("stream partitions %zu sizes", stream.size());
+    for (auto& part : stream) std::printf(" %u", part.second);
+    std::printf(" last (%u,%u) (%u,%u)\n", std::get<0>(stream.back().first[0]), std::get<1>(stream.back().first[0]),
+                std::get<0>(stream.back().first[1]), std::get<1>(stream.back().first[1]));
+    for (auto& part : stream) delete[] part.first;
+    try { read_unweighted_graph(stream_path.c_str(), true); }
+    catch (const std::exception& e) { std::printf("bad file: %s\n", e.what()); }
+    std::fflush(stdout);
+}
+
+int main(int argc, char** argv_main)
+{
+    if (argc > 1) text_formats(argv_main[1]);
     // rows: 0:{1,2} 1:{0,2,3} 2:{0,1,3,4,5} 3:{1,2,5} 4:{2,5} 5:{2,3,4}
     const uintV adj[] = {1, 2, 0, 2, 3, 0, 1, 3, 4, 5, 1, 2, 5, 2, 5, 2, 3, 4};
     const uintE off[] = {0, 2, 5, 10, 13, 15};
@@ -40,6 +70,18 @@ int main()
     std::printf("delete affected %zu edges %zu\n", affected.size(), wharf.number_of_edges());
     dump("deleted");
     pbbs::free_array(batch);
+
+    if (argc > 1)
+    {
+        const std::string walks_path = std::string(argv_main[1]) + "/walks.txt";
+        const size_t bytes = wharf.write_walks(walks_path.c_str(), affected);                // vertex-classification.cpp:167-178
+        std::ifstream f(walks_path);
+        std::string line;
+        size_t lines = 0;
+        bool same = true;
+        while (std::getline(f, line)) same = same && line == wharf.walk(affected[lines++]);
+        std::printf("walks.txt %zu bytes %zu lines same %d\n", bytes, lines, (int) same);
+    }
 
     auto flat = wharf.flatten_graph();
     std::printf("degree(2) = %zu\n", (size_t) flat[2].degree);

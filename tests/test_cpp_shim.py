@@ -20,19 +20,28 @@ def build_driver() -> Path:
     return exe
 
 
-def test_cpp_shim_compiles_and_fails_loudly_without_gpu():
+def check_text_formats(out):
+    assert "adjacency n 3 m 4 offsets 0 2 3 edges 1 2 0 0" in out                        # read_unweighted_graph, IO.h:67
+    assert "stream partitions 3 sizes 4 4 2 last (4,5) (5,4)" in out                      # create_edge_stream, vertex-classification.cpp:5
+    assert any(l.startswith("bad file: ") and "not an AdjacencyGraph" in l for l in out)
+
+
+def test_cpp_shim_compiles_and_fails_loudly_without_gpu(tmp_path):
     exe = build_driver()
     import torch
     if torch.cuda.is_available():
         pytest.skip("GPU present: covered by test_cpp_shim_reproduces_reference_corpora")
-    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    r = subprocess.run([str(exe), str(tmp_path)], capture_output=True, text=True)
     assert r.returncode != 0 and "no CPU path" in r.stderr          # no silent fallback
+    check_text_formats(r.stdout.splitlines())                       # host-only part ran before the engine was constructed
 
 
 @pytest.mark.gpu
-def test_cpp_shim_reproduces_reference_corpora():
+def test_cpp_shim_reproduces_reference_corpora(tmp_path):
     exe = build_driver()
-    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines()
+    out = subprocess.run([str(exe), str(tmp_path)], capture_output=True, text=True, check=True).stdout.splitlines()
+    check_text_formats(out)
+    assert any(l.startswith("walks.txt ") and l.endswith(" 12 lines same 1") for l in out)   # write_walks == walk() + endl per affected walk
     six = json.loads((ROOT / "tests" / "golden" / "golden.json").read_text())["six"]
     for tag, walks in zip(("initial", "inserted", "deleted"), six["walks"]):
         got = [l.split(": ", 1)[1] for l in out if l.startswith(tag + " ")]

@@ -1,0 +1,198 @@
+"""Ingest and export either side of the path (dynamicgraphrepresentationlearning_b200/graph_io.py,
+wmh_parse_* / wmh_format_* / wmh_write_walks in include/wharfmh_b200.h).
+
+Pinned to the reference's own tools: tests/golden/io_golden.json holds what experiments/bin/SNAPtoAdj -s writes for
+experiments/data/cora-graph (tests/golden/make_io_golden.py), tests/golden/golden.json the FNV-1a of the text the
+unmodified reference prints for the cora corpus (WharfMH::walk of every walk + newline).  The text functions are host
+code and run without a GPU; the set work of ingest is the engine's batch insert and is marked gpu."""
+import hashlib
+import json
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_DIR
+
+
+@pytest.fixture(scope="module")
+def gio(wharf):
+    from dynamicgraphrepresentationlearning_b200 import graph_io
+    return graph_io
+
+
+@pytest.fixture(scope="module")
+def io_golden():
+    return json.loads((GOLDEN_DIR / "io_golden.json").read_text())
+
+
+@pytest.fixture(scope="module")
+def cora_pairs():
+    return np.load(GOLDEN_DIR / "cora_edge_list.npz")["pairs"]
+
+
+def fnv1a(data: bytes) -> int:
+    h = 0xCBF29CE484222325
+    for c in data:
+        h = ((h ^ c) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def edge_list_text(pairs) -> bytes:
+    return "".join(f"{u} {v}\n" for u, v in pairs.tolist()).encode()
+
+
+# ---- host text functions (no GPU) -----------------------------------------------------------------------------------
+def test_adjacency_graph_text_equals_snaptoadj(gio, io_golden, cora, tmp_path):
+    n, off, adj = cora
+    text = gio.format_unweighted_graph(off, adj)
+    assert len(text) == io_golden["cora_adj_bytes"] and hashlib.sha256(text).hexdigest() == io_golden["cora_adj_sha256"]
+    n2, m2, off2, adj2 = gio.read_unweighted_graph(text)
+    assert (n2, m2) == (n, adj.shape[0]) and off2.dtype == np.uint64 and adj2.dtype == np.uint32
+    assert np.array_equal(off2, off) and np.array_equal(adj2, adj)          # n offsets, no n+1-th (IO.h:97)
+    path = tmp_path / "cora.adj"
+    gio.write_unweighted_graph(path, np.append(off, np.uint64(adj.shape[0])), adj, row_ptr=True)
+    assert path.read_bytes() == text
+    assert gio.read_unweighted_graph(path)[0] == n
+    toy = gio.read_unweighted_graph(io_golden["toy_adj"].encode())
+    assert toy[:2] == (5, 6) and toy[2].tolist() == [0, 2, 3, 3, 5] and toy[3].tolist() == [3, 4, 3, 0, 1, 0]
+    assert gio.format_unweighted_graph(toy[2], toy[3]).decode() == io_golden["toy_adj"]
+    assert gio.read_unweighted_graph(b"  AdjacencyGraph\t0\r\n0\n")[:2] == (0, 0)
+    assert gio.format_unweighted_graph(np.empty(0), np.empty(0)) == b"AdjacencyGraph\n0\n0\n"
+
+
+@pytest.mark.parametrize("text,what", [
+    (b"Adjacency 1 0 0", "not an AdjacencyGraph"), (b"AdjacencyGraphX 0 0", "not an AdjacencyGraph"), (b"", "not an AdjacencyGraph"),
+    (b"AdjacencyGraph", "vertex count"), (b"AdjacencyGraph 3", "edge count"),
+    (b"AdjacencyGraph 2 1 0 1", "fewer than n"), (b"AdjacencyGraph 2 1 0 1 1 1", "more than n"),
+    (b"AdjacencyGraph 2 1 1 0 1", "non-decreasing"), (b"AdjacencyGraph 2 1 0 2 1", "non-decreasing"),
+    (b"AdjacencyGraph 2 1 0 1 2", "neighbour id >= n"), (b"AdjacencyGraph 2 1 0 x 1", "fewer than")])
+def test_adjacency_graph_rejects_bad_files(wharf, gio, text, what):
+    with pytest.raises(wharf.WharfError, match=what):              # reference: assert / garbage (IO.h:87,94)
+        gio.read_unweighted_graph(text)
+
+
+def test_edge_list_parser(wharf, gio, io_golden, cora_pairs, tmp_path):
+    text = edge_list_text(cora_pairs)
+    assert hashlib.sha256(text).hexdigest() == io_golden["cora_edge_list_sha256"]       # the fixture IS the reference's file
+    pairs, vertices = gio.read_edge_list(text)
+    assert vertices == 2708 and pairs.dtype == np.uint32 and np.array_equal(pairs, cora_pairs)
+    path = tmp_path / "cora-graph"
+    path.write_bytes(text)
+    assert np.array_equal(gio.read_edge_list(path)[0], cora_pairs)
+    pairs, vertices = gio.read_edge_list(b"# SNAP header\n3 1\r\n\n1\t3\n  2 2  \n%x\n0 3")     # no final newline
+    assert pairs.tolist() == [[3, 1], [1, 3], [2, 2], [0, 3]] and vertices == 4
+    assert gio.read_edge_list(io_golden["toy_edge_list"].encode())[0].tolist() == [[3, 1], [1, 3], [2, 2], [0, 3], [0, 3], [4, 0]]
+    empty, vertices = gio.read_edge_list(b"# nothing\n\n")
+    assert empty.shape == (0, 2) and vertices == 0
+    assert gio.read_edge_list(b"4294967293 0\n")[1] == 4294967294
+    for bad, code in ((b"1 2 3\n", 1), (b"1\n", 1), (b"a b\n", 1), (b"1 -2\n", 1), (b"0 1\n1 4294967295\n", 5), (b"1 99999999999999999999999\n", 1)):
+        with pytest.raises(wharf.WharfError) as err:
+            gio.read_edge_list(bad)
+        assert err.value.code == code
+    with pytest.raises(wharf.WharfError, match="line 3"):
+        gio.read_edge_list(b"# c\n0 1\n0 x\n")
+    # the C entry point reports the count when the buffer is too small
+    import ctypes as C
+    lib = wharf._capi.load()
+    k, v = C.c_uint64(), C.c_uint64()
+    small = np.zeros((2, 2), dtype=np.uint32)
+    rc = lib.wmh_parse_edge_list(b"0 1\n2 3\n4 5\n", 12, small.ctypes.data, 2, C.byref(k), C.byref(v))
+    assert rc == wharf._capi.ERR_RANGE and k.value == 3 and small.tolist() == [[0, 1], [2, 3]]
+
+
+def test_walk_text_equals_reference_corpus_text(gio, golden, cora, wo):
+    n, off, adj = cora
+    o = wo.Oracle(n, off, adj, walks_per_vertex=10, walk_length=80)
+    o.generate()
+    text = gio.format_walks(o.walks())
+    assert fnv1a(text) == golden["cora"]["phases"][0]["corpus_fnv1a"]       # what the unmodified reference prints
+    assert text.startswith(b"0 435 258 268 616 438 710 847 1032 848 ") and text.count(b"\n") == 10 * n
+    o.close()
+    rows = np.array([[1, 2, 0xFFFFFFFF], [0xFFFFFFFF] * 3, [4294967294, 0, 7]], dtype=np.uint32)
+    assert gio.format_walks(rows) == b"1 2 \n\n4294967294 0 7 \n"             # a stopped walker ends its line early
+    assert gio.format_walks(np.empty((0, 80), dtype=np.uint32)) == b""
+    rng = np.random.default_rng(3)
+    rows = rng.integers(0, 2 ** 32 - 1, size=(200, 17), dtype=np.uint64).astype(np.uint32)
+    assert gio.format_walks(rows).decode() == "".join("".join(f"{v} " for v in r) + "\n" for r in rows.tolist())
+
+
+def test_create_edge_stream_follows_the_reference_loop(gio, cora_pairs, tmp_path):
+    def reference_loop(pairs, eps):                # vertex-classification.cpp:14-27, restated
+        temp = []
+        for it, (a, b) in enumerate(pairs.tolist()):
+            if it % eps == 0:
+                temp.append([])
+            temp[-1].append((a, b))
+            temp[-1].append((b, a))
+        return temp
+    for eps in (5000, 1000, 5429, 7):
+        stream = gio.create_edge_stream(cora_pairs, eps)
+        want = reference_loop(cora_pairs, eps)
+        assert len(stream) == len(want)
+        assert all(s.dtype == np.uint32 and s.tolist() == [list(p) for p in w] for s, w in zip(stream, want))
+    path = tmp_path / "stream"
+    path.write_bytes(edge_list_text(cora_pairs[:11]))
+    assert [s.shape[0] for s in gio.create_edge_stream(path, 4)] == [8, 8, 6]
+    assert gio.create_edge_stream(np.empty((0, 2), dtype=np.uint32)) == []
+    with pytest.raises(ValueError):
+        gio.create_edge_stream(cora_pairs, 0)
+
+
+# ---- through the engine (GPU) ---------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_snap_to_adj_equals_the_reference_tool(wharf, gio, io_golden, cora, cora_pairs):
+    n, off, adj = cora
+    got_n, got_m, got_off, got_adj = gio.snap_to_adj(cora_pairs)
+    assert (got_n, got_m) == (n, adj.shape[0]) and np.array_equal(got_off, off) and np.array_equal(got_adj, adj)
+    assert hashlib.sha256(gio.format_unweighted_graph(got_off, got_adj)).hexdigest() == io_golden["cora_adj_sha256"]
+    _, _, toy_off, toy_adj = gio.snap_to_adj(io_golden["toy_edge_list"].encode())            # comment, loop, duplicates
+    assert gio.format_unweighted_graph(toy_off, toy_adj).decode() == io_golden["toy_adj"]
+    # directed: rows are sets here (WharfMH needs unique rows, wharfmh.h:58); loops dropped
+    _, m, d_off, d_adj = gio.snap_to_adj(cora_pairs, symmetric=False)
+    keys = np.unique(cora_pairs[:, 0].astype(np.int64) << 32 | cora_pairs[:, 1].astype(np.int64))
+    assert m == keys.shape[0] and np.array_equal(np.repeat(np.arange(n), np.diff(np.append(d_off, np.uint64(m)).astype(np.int64))) << 32 | d_adj.astype(np.int64), keys)
+    assert gio.snap_to_adj(np.empty((0, 2), dtype=np.uint32))[:2] == (0, 0)
+
+
+@pytest.mark.gpu
+def test_stream_ingest_and_walks_txt(wharf, gio, golden, cora, cora_pairs, wo, tmp_path):
+    """The vertex-classification pipeline's shape (vertex-classification.cpp:136-197): a graph grown from an edge stream,
+    the walks each batch changed handed over as text."""
+    n, off, adj = cora
+    cfg = wharf.Config(walks_per_vertex=10, walk_length=80, random_walk_model=wharf.DEEPWALK, deterministic_mode=True)
+    # the whole file as one stream == SNAPtoAdj -s; its corpus text == what the unmodified reference prints
+    with gio.graph_from_edge_list(cora_pairs, config=cfg) as e:
+        assert e.number_of_vertices() == n and e.number_of_edges() == adj.shape[0]
+        e.generate_initial_random_walks()
+        path = tmp_path / "walks.txt"
+        written = gio.write_walks(e, path, np.arange(10 * n, dtype=np.uint64))
+        text = path.read_bytes()
+        assert written == len(text) and fnv1a(text) == golden["cora"]["phases"][0]["corpus_fnv1a"]
+        b = wo.generate_batch(100, n, 0, False, False)
+        affected = e.insert_edges_batch(b.copy(), sorted=True, remove_dups=False)
+        assert gio.write_walks(e, path, affected) > 0
+        lines = path.read_bytes().split(b"\n")
+        assert len(lines) == affected.shape[0] + 1 and lines[-1] == b""
+        for k in (0, 1, affected.shape[0] // 2, affected.shape[0] - 1):
+            assert lines[k].decode() == e.walk(int(affected[k]))                      # WharfMH::walk + endl per affected walk
+        before = path.stat().st_size
+        gio.write_walks(e, path, affected[:3], append=True)
+        assert path.read_bytes()[before:] == b"".join(lines[:3][i] + b"\n" for i in range(3))
+        assert fnv1a(gio.format_walks(e.walks())) == golden["cora"]["phases"][1]["corpus_fnv1a"]
+        with pytest.raises(wharf.WharfError):
+            gio.write_walks(e, path, np.array([10 * n], dtype=np.uint64))             # not a walk of this engine
+    # grown batch by batch, the graph ends the same; a sharded engine writes only walks it holds
+    with wharf.WharfMH(n, config=cfg) as e:
+        with pytest.raises(wharf.WharfError):
+            gio.write_walks(e, tmp_path / "none.txt", np.array([0], dtype=np.uint64))  # no corpus yet
+        for batch in gio.create_edge_stream(cora_pairs, 1000):
+            e.insert_edges_batch(batch, sorted=False, remove_dups=True)
+        rp, col = e.flatten_graph()
+        assert np.array_equal(rp[:-1], off) and np.array_equal(col, adj)
+    shard = wharf.Config(walks_per_vertex=10, walk_length=80, deterministic_mode=True, rank=1, world=2)
+    with wharf.WharfMH(n, adj.shape[0], off, adj, config=shard) as e:
+        e.generate_initial_random_walks()
+        mine = e.local_walk_ids()
+        assert gio.write_walks(e, tmp_path / "shard.txt", mine[:5]) > 0
+        with pytest.raises(wharf.WharfError, match="not held"):
+            gio.write_walks(e, tmp_path / "shard.txt", np.array([0], dtype=np.uint64))

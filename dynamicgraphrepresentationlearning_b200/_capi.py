@@ -104,6 +104,7 @@ SIGNATURES = {
     "wmh_build_index": (i32, [vp]),
     "wmh_index_find_next": (i32, [vp, u32, u64, u32, PU32, C.POINTER(i32)]),
     "wmh_index_size": (i32, [vp, u32, PU64]),
+    "wmh_index_sizes": (i32, [vp, vp]),
     "wmh_szudzik_pair_u64": (i32, [i32, vp, vp, vp, u64, PU64]),
     "wmh_szudzik_unpair_u64": (i32, [i32, vp, vp, vp, u64]),
     "wmh_szudzik_pair_u32": (i32, [i32, vp, vp, vp, u64, PU64]),
@@ -129,6 +130,7 @@ SIGNATURES = {
     "wmh_peer_bytes_needed": (u64, [vp]),
     "wmh_peer_exchanges": (u64, [vp]),
     "wmh_generate_batch_of_edges_device": (i32, [i32, u64, u64, u64, i32, i32, C.c_double, C.c_double, C.c_double, vp, PU64]),
+    "wmh_generate_batch_of_edges": (i32, [i32, u64, u64, u64, i32, i32, C.c_double, C.c_double, C.c_double, vp, u64, PU64]),
     "wmh_pairs_to_csr_device": (i32, [i32, u64, vp, u64, vp, vp]),
 }
 

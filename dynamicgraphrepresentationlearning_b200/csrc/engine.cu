@@ -1068,6 +1068,26 @@ int wmh_index_size(wmh_engine* e, uint32_t vertex, uint64_t* entries)
     });
 }
 
+int wmh_index_sizes(wmh_engine* e, uint64_t* entries)
+{
+    if (!e || !entries) return fail(WMH_ERR_INVALID, "null argument");
+    const u64 n = e->g.n;
+    if (!e->have_walks)                                          // no corpus: every vertex's index is empty (wharfmh.h:237-245)
+    {
+        std::fill(entries, entries + n, 0ull);
+        return WMH_OK;
+    }
+    return guarded([&] {
+        e->bind();
+        ensure_index(*e);
+        std::vector<u64> ptr(n + 1);
+        WHARF_CUDA(cudaMemcpyAsync(ptr.data(), e->index.ptr.ptr, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        for (u64 v = 0; v < n; v++) entries[v] = ptr[v + 1] - ptr[v];
+        return (int) WMH_OK;
+    });
+}
+
 int wmh_compressed_walks(wmh_engine* e, uint64_t* ptr, uint64_t* codes, uint64_t capacity, uint64_t* total)
 {
     if (!e) return fail(WMH_ERR_INVALID, "null engine");
@@ -1265,6 +1285,26 @@ int wmh_generate_batch_of_edges_device(int device, uint64_t edges_number, uint64
         DefaultCtx ctx(device);
         u64 kept = 0;
         rmat_generate_device(ctx.lc, edges_number, vertices_number, batch_seed, self_loops != 0, directed != 0, a, b, c, d_out, &kept);
+        *count = kept;
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_generate_batch_of_edges(int device, uint64_t edges_number, uint64_t vertices_number, uint64_t batch_seed, int self_loops, int directed,
+                                double a, double b, double c, uint32_t* out, uint64_t capacity, uint64_t* count)
+{
+    if (!count || (edges_number && !out)) return fail(WMH_ERR_INVALID, "null argument");
+    if (vertices_number < 2) return fail(WMH_ERR_INVALID, "vertices_number must be >= 2");
+    if (a + b + c > 1) return fail(WMH_ERR_INVALID, "a + b + c add to more than 1");      // rmat_util.h:16
+    const u64 slots = edges_number * (directed ? 1 : 2);
+    if (capacity < slots) return fail(WMH_ERR_RANGE, "out must hold edges_number pairs (twice that when not directed)");
+    return guarded([&] {
+        DefaultCtx ctx(device);
+        Scratch<u32> d_pairs(nullptr, 2 * slots);
+        u64 kept = 0;
+        rmat_generate_device(ctx.lc, edges_number, vertices_number, batch_seed, self_loops != 0, directed != 0, a, b, c, d_pairs.ptr, &kept);
+        if (kept) WHARF_CUDA(cudaMemcpyAsync(out, d_pairs.ptr, kept * 2 * sizeof(u32), cudaMemcpyDeviceToHost, nullptr));
+        WHARF_CUDA(cudaStreamSynchronize(nullptr));
         *count = kept;
         return (int) WMH_OK;
     });

@@ -263,6 +263,12 @@ class WharfMH:
         check(self._lib.wmh_index_find_next(self._h, vertex, walk_id, position, C.byref(nxt), C.byref(found)))
         return int(nxt.value), bool(found.value)
 
+    def index_sizes(self) -> np.ndarray:
+        """Entries of every vertex's inverted index (all zero while no corpus exists)."""
+        out = np.empty(self.number_of_vertices(), dtype=np.uint64)
+        check(self._lib.wmh_index_sizes(self._h, _ptr(out)))
+        return out
+
     def index_size(self, vertex: int) -> int:
         k = C.c_uint64()
         check(self._lib.wmh_index_size(self._h, vertex, C.byref(k)))

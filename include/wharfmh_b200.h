@@ -224,6 +224,9 @@ WMH_API int wmh_index_find_next(wmh_engine* e, uint32_t vertex, uint64_t walk_id
                                 uint32_t* next, int* found);
 /* Number of index entries stored at `vertex` (InvertedIndex::size()). */
 WMH_API int wmh_index_size(wmh_engine* e, uint32_t vertex, uint64_t* entries);
+/* The same for every vertex at once (entries[n]); all zero while no corpus exists (what flatten_vertex_tree,
+ * graph/wharfmh.h:140, shows of each vertex's inverted_index after construction and after destroy_index). */
+WMH_API int wmh_index_sizes(wmh_engine* e, uint64_t* entries);
 
 /* ---- Szudzik pairing (walks/pairings.h) and the paired corpus (walks/compressed_walks.h) --------- */
 
@@ -305,6 +308,11 @@ WMH_API uint64_t wmh_peer_exchanges(const wmh_engine* e);
 WMH_API int wmh_generate_batch_of_edges_device(int device, uint64_t edges_number, uint64_t vertices_number,
                                                uint64_t batch_seed, int self_loops, int directed,
                                                double a, double b, double c, uint32_t* d_out, uint64_t* count);
+/* The same with the pairs returned to host memory (what utility::generate_batch_of_edges hands its callers,
+ * throughput-latency.cpp:121-123): out holds `capacity` pairs, capacity >= edges_number*(directed?1:2). */
+WMH_API int wmh_generate_batch_of_edges(int device, uint64_t edges_number, uint64_t vertices_number,
+                                        uint64_t batch_seed, int self_loops, int directed,
+                                        double a, double b, double c, uint32_t* out, uint64_t capacity, uint64_t* count);
 /* Builds CSR (d_offsets[n+1] u64) from sorted (src,dst) pairs on the device. */
 WMH_API int wmh_pairs_to_csr_device(int device, uint64_t n, const uint32_t* d_pairs, uint64_t count,
                                     uint64_t* d_offsets, uint32_t* d_edges);

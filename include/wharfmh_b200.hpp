@@ -67,6 +67,24 @@ namespace pbbs
     };
 }
 
+namespace pbbs
+{
+    // pbbslib/seq.h delayed_sequence: element i is f(i), computed on access
+    template <class T, class F>
+    struct delayed_sequence
+    {
+        size_t n;
+        F f;
+        size_t size() const { return n; }
+        T operator[](size_t i) const { return f(i); }
+    };
+    template <class T, class F> delayed_sequence<T, F> delayed_seq(size_t n, F f) { return delayed_sequence<T, F>{n, std::move(f)}; }
+}
+
+// pbbslib/parallel.h parallel_for: host-side loops of the callers are not the hot path here - they run in order
+template <class F>
+inline void parallel_for(size_t start, size_t end, F f, long /*granularity*/ = 0, bool /*conservative*/ = false) { for (size_t i = start; i < end; i++) f(i); }
+
 // pbbslib/get_time.h:9-81
 struct timer
 {
@@ -161,6 +179,73 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
         std::vector<uintV> col_;
     };
 
+    // graph/wharfmh.h:140 (flatten_vertex_tree) / graph/vertex.h: what the reference's tests read of a vertex entry -
+    // its neighbours, the size of its inverted index and of its sampler manager (tests/wharfmh.cpp:65-99,114-118,134-139).
+    struct VertexEntryView
+    {
+        struct Edges                                                     // tree_plus edge list of the vertex
+        {
+            const uintV* row = nullptr;
+            size_t count = 0;
+            size_t degree() const { return count; }
+            size_t size() const { return count; }
+            uintV* get_edges(uintV /*source*/) const                     // a fresh array the caller may free with pbbs::free_array
+            {
+                uintV* out = pbbs::new_array_no_init<uintV>(count);
+                if (count) std::memcpy(out, row, count * sizeof(uintV));
+                return out;
+            }
+        } compressed_edges;
+        struct Index                                                     // walks/inverted_index.h
+        {
+            const void* root = nullptr;                                  // nullptr <=> empty, as the PAM map's root
+            size_t entries = 0;
+            size_t size() const { return entries; }
+        } inverted_index;
+        struct Samplers                                                  // graph/vertex.h:12 SamplerManager
+        {
+            bool untouched = true;
+            // Exact while no Metropolis-Hastings walk can have run (deterministic mode).  Afterwards the states live in
+            // the aux words of the device rows, keyed by edge, and are not counted per vertex.
+            size_t size() const
+            {
+                if (!untouched) throw std::logic_error("wharfmh_b200: sampler states are kept per edge on the device, not per vertex");
+                return 0;
+            }
+        } samplers;
+        const Samplers* sampler_manager = nullptr;
+    };
+
+    class FlatVertexTree
+    {
+    public:
+        FlatVertexTree() = default;
+        FlatVertexTree(std::vector<uintE> row_ptr, std::vector<uintV> col, const std::vector<uint64_t>& index_sizes, bool samplers_untouched)
+            : row_ptr_(std::move(row_ptr)), col_(std::move(col)), entries_(index_sizes.size())
+        {
+            for (size_t v = 0; v < entries_.size(); v++)
+            {
+                auto& e = entries_[v];
+                e.compressed_edges.row = col_.data() + row_ptr_[v];
+                e.compressed_edges.count = row_ptr_[v + 1] - row_ptr_[v];
+                e.inverted_index.entries = index_sizes[v];
+                e.inverted_index.root = index_sizes[v] ? static_cast<const void*>(&e) : nullptr;
+                e.samplers.untouched = samplers_untouched;
+            }
+            for (auto& e : entries_) e.sampler_manager = &e.samplers;
+        }
+        FlatVertexTree(const FlatVertexTree&) = delete;
+        FlatVertexTree& operator=(const FlatVertexTree&) = delete;
+        FlatVertexTree(FlatVertexTree&&) = default;                      // vectors keep their buffers: the views stay valid
+        size_t size() const { return entries_.size(); }
+        const VertexEntryView& operator[](size_t v) const { return entries_[v]; }
+        size_t size_in_bytes() const { return row_ptr_.size() * sizeof(uintE) + col_.size() * sizeof(uintV) + entries_.size() * sizeof(VertexEntryView); }
+    private:
+        std::vector<uintE> row_ptr_;
+        std::vector<uintV> col_;
+        std::vector<VertexEntryView> entries_;
+    };
+
     // graph/wharfmh.h:21
     class WharfMH
     {
@@ -197,6 +282,26 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
             std::vector<uintV> col(number_of_edges());
             detail::check(wmh_flatten_graph(engine_, row_ptr.data(), col.data()));
             return FlatGraph(std::move(row_ptr), std::move(col));
+        }
+
+        [[nodiscard]] FlatVertexTree flatten_vertex_tree() const                                       // :140
+        {
+            if (!engine_) return FlatVertexTree();                                                      // destroyed: no vertices (tests/wharfmh.cpp:114-117)
+            const size_t n = number_of_vertices();
+            std::vector<uintE> row_ptr(n + 1);
+            std::vector<uintV> col(number_of_edges());
+            std::vector<uint64_t> index_sizes(n);
+            detail::check(wmh_flatten_graph(engine_, row_ptr.data(), col.data()));
+            detail::check(wmh_index_sizes(engine_, index_sizes.data()));
+            return FlatVertexTree(std::move(row_ptr), std::move(col), index_sizes, config::deterministic_mode);
+        }
+
+        // :219.  map_function(entry, i) with entry.first = the vertex and entry.second = its entry, in vertex order.
+        template <class Function>
+        void map_vertices(Function map_function, bool /*run_seq*/ = false, size_t /*granularity*/ = 0) const
+        {
+            const FlatVertexTree flat = flatten_vertex_tree();
+            for (size_t v = 0; v < flat.size(); v++) map_function(std::pair<types::Vertex, const VertexEntryView&>(static_cast<types::Vertex>(v), flat[v]), v);
         }
 
         void destroy()                                                                                  // :228
@@ -362,6 +467,18 @@ namespace detail
     }
 }
 
+inline std::pair<std::tuple<uintV, uintV>*, size_t> utility::generate_batch_of_edges(size_t edges_number, size_t vertices_number, size_t batch_seed, bool self_loops,
+                                                                                     bool directed, double a, double b, double c, bool /*run_seq*/)
+{
+    const size_t slots = edges_number * (directed ? 1 : 2);
+    std::vector<uint32_t> pairs(2 * slots);
+    uint64_t kept = 0;
+    dygrl::detail::check(wmh_generate_batch_of_edges(config::device, edges_number, vertices_number, batch_seed, self_loops, directed, a, b, c, pairs.data(), slots, &kept));
+    auto* edges = pbbs::new_array_no_init<std::tuple<uintV, uintV>>(kept);      // the caller frees it with pbbs::free_array (throughput-latency.cpp:146)
+    for (size_t i = 0; i < kept; i++) new (edges + i) std::tuple<uintV, uintV>(pairs[2 * i], pairs[2 * i + 1]);
+    return {edges, static_cast<size_t>(kept)};
+}
+
 // libs/compressed_trees/common/IO.h:67-106: Ligra "AdjacencyGraph" text format -> (n, m, offsets[n], edges[m])
 inline std::tuple<size_t, size_t, uintE*, uintV*> read_unweighted_graph(const char* fname, bool /*is_symmetric*/, bool /*mmap*/ = false)
 {
@@ -381,8 +498,9 @@ inline std::tuple<size_t, size_t, uintE*, uintV*> read_unweighted_graph(const ch
     return {n, m, offsets, edges};
 }
 
-// experiments/src/vertex-classification.cpp:5-38: the lines "u v" of file -f in partitions of -eps lines, every line as
-// (u, v) and (v, u); each partition is a heap array the caller passes to insert_edges_batch(size, array, false, true).
+// experiments/src/vertex-classification.cpp:5-38: the lines "u v" of a file in partitions of edge_partition_size lines, every
+// line as (u, v) and (v, u); each partition is a heap array the caller passes to insert_edges_batch(size, array, false, true).
+// (The driver defines create_edge_stream(commandLine&, stream) itself - -f and -eps options - so that signature is left to it.)
 inline void create_edge_stream(const char* fname, size_t edge_partition_size, std::vector<std::pair<std::tuple<uintV, uintV>*, uintV>>& stream)
 {
     if (edge_partition_size == 0) throw std::invalid_argument("edge partition size must be positive");
@@ -418,12 +536,5 @@ struct commandLine
     long getOptionLongValue(const std::string& option, long def) const { char* v = getOptionValue(option); return v ? std::atol(v) : def; }
     double getOptionDoubleValue(const std::string& option, double def) const { char* v = getOptionValue(option); return v ? std::atof(v) : def; }
 };
-
-// The reference's own signature (vertex-classification.cpp:5): file from -f (default "stream"), partition size from -eps (5000).
-inline void create_edge_stream(commandLine& command_line, std::vector<std::pair<std::tuple<uintV, uintV>*, uintV>>& stream)
-{
-    const std::string fname = command_line.getOptionValue("-f", "stream");
-    create_edge_stream(fname.c_str(), static_cast<size_t>(command_line.getOptionLongValue("-eps", 5000)), stream);
-}
 
 #endif  // WHARFMH_B200_HPP

@@ -19,12 +19,8 @@ static void text_formats(const std::string& dir)
     pbbs::free_array(goff);
     pbbs::free_array(gadj);
     { std::ofstream f(stream_path); f << "# five lines\n0 1\n1 2\n2 3\n3 4\n4 5\n"; }
-    char a0[] = "driver", a1[] = "-f", a3[] = "-eps", a4[] = "2";
-    std::string a2 = stream_path;
-    char* argv[] = {a0, a1, a2.data(), a3, a4};
-    commandLine cl(5, argv);
     std::vector<std::pair<std::tuple<uintV, uintV>*, uintV>> stream;
-    create_edge_stream(cl, stream);                                                           // vertex-classification.cpp:5
+    create_edge_stream(stream_path.c_str(), 2, stream);                                       // vertex-classification.cpp:5 with -eps 2
     std::printf("stream partitions %zu sizes", stream.size());
     for (auto& part : stream) std::printf(" %u", part.second);
     std::printf(" last (%u,%u) (%u,%u)\n", std::get<0>(stream.back().first[0]), std::get<1>(stream.back().first[0]),

@@ -1,0 +1,107 @@
+"""The drop-in claim, checked with the reference's own callers (SURVEY 8b "Callers of the boundary").
+
+include/compat/ holds forwarding headers with the reference's header names (wharfmh.h, pairings.h, pbbslib/...), so the
+reference's experiment drivers and test files compile UNCHANGED against include/wharfmh_b200.hpp and link
+libwharfmh_b200.so - no line of them is edited or copied; they are compiled where they lie under /root/reference
+(tests/cpp/build_reference_callers.py, also run by __graft_entry__.build()).  The binaries land in tests/cpp/_build/
+(git-ignored, but they travel to the GPU box like the library):
+
+  * here (no GPU): all four experiments/src drivers and tests/wharfmh.cpp compile and link; tests/pairings.cpp also RUNS -
+    its known-answer and 10 M round-trip tests pass against the library's pairing functions;
+  * on the B200: the reference's throughput-latency driver runs on cora and the affected-walk counts it prints equal the
+    CPU oracle's replay of the same batch sequence; memory-footprint runs to completion.
+googletest is not installed: tests/cpp/mini_gtest/ is a 60-line runner with its spelling (test infrastructure)."""
+import re
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT / "tests" / "cpp"))
+import build_reference_callers as brc  # noqa: E402
+
+needs_reference = pytest.mark.skipif(not brc.reference_present(), reason="/root/reference is not on this machine")
+
+
+@needs_reference
+def test_reference_drivers_and_tests_compile_unchanged():
+    built = brc.build_all()
+    assert {p.name for p in built} == {"throughput-latency", "memory-throughput-latency", "memory-footprint", "vertex-classification",
+                                       "ref_test_wharfmh", "ref_test_pairings"}
+    assert all(p.exists() for p in built)
+    # nothing of the reference was copied next to the binaries or into the compat headers
+    assert not list((ROOT / "tests" / "cpp" / "_build" / "ref_callers").glob("*.cpp"))
+    for header in (ROOT / "include" / "compat").rglob("*.h"):
+        assert len(header.read_text().splitlines()) < 60, header
+
+
+@needs_reference
+def test_reference_pairing_tests_pass_against_the_library():
+    brc.build_all()
+    r = subprocess.run([str(brc.OUT / "ref_test_pairings")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "[  TOTAL   ] 4 tests, 0 failures" in r.stdout
+    assert "Encoded value (Szudzik pairing): 4294967295" in r.stdout and "Decoded value (Szudzik pairing): 65535 65535" in r.stdout   # tests/pairings.cpp:29-37
+    assert "Encoded value (Szudzik pairing for triplets): 229643916" in r.stdout                                                      # :75-90
+    assert "Decoded value (Szudzik pairing for triplets): 123 25 200" in r.stdout
+    assert "failed" not in r.stderr                     # the 10 M round trips report mismatches on stderr (:61-64, :113-117)
+
+
+def test_drivers_fail_loudly_without_gpu(tmp_path):
+    exe = brc.OUT / "memory-footprint"
+    if not exe.exists():
+        pytest.skip("reference callers not built on this machine")
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from dynamicgraphrepresentationlearning_b200 import graph_io
+    z = np.load(ROOT / "tests" / "golden" / "cora_graph.npz")
+    graph_io.write_unweighted_graph(tmp_path / "cora.adj", z["offsets"], z["edges"])
+    r = subprocess.run([str(exe), "-f", str(tmp_path / "cora.adj")], capture_output=True, text=True)
+    assert "Vertices: 2708 Edges: 10556" in r.stdout                    # the reader ran (host code) ...
+    assert r.returncode != 0 and "no CPU path" in r.stderr              # ... the engine refused to
+
+
+@pytest.mark.gpu
+def test_reference_throughput_latency_driver_on_gpu(wharf, wo, cora, tmp_path):
+    exe = brc.OUT / "throughput-latency"
+    if not exe.exists():
+        pytest.skip("reference callers were not built where the snapshot was taken")
+    from dynamicgraphrepresentationlearning_b200 import graph_io
+    n, off, adj = cora
+    graph_io.write_unweighted_graph(tmp_path / "cora.adj", off, adj)
+    r = subprocess.run([str(exe), "-f", str(tmp_path / "cora.adj"), "-w", "10", "-l", "80", "-trials", "1"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Walking model: DEEPWALK" in r.stdout and "Vertices: 2708 Edges: 10556" in r.stdout
+    got = [float(x) for x in re.findall(r"Average number of walks affected = ([0-9.e+]+)", r.stdout)]
+    batch_sizes = [int(x) for x in re.findall(r"Batch size = \d+ \| (\d+) ", r.stdout)]
+    # the same sequence on the CPU oracle: generate, then per batch size insert + delete of generate_batch_of_edges(size, n, 0, false, true)
+    o = wo.Oracle(n, off, adj, walks_per_vertex=10, walk_length=80)
+    o.generate()
+    want, sizes = [], []
+    for size in (5, 50, 500):                                           # throughput-latency.cpp:87-90
+        b = wo.generate_batch(size, n, 0, False, True)
+        sizes.append(b.shape[0])
+        for delete in (False, True):
+            o.update(b.copy(), delete=delete, remove_dups=True)
+            want.append(float(o.affected()[0].shape[0]))
+    o.close()
+    assert batch_sizes == sizes
+    assert got == want
+    assert "Average time to generate random walks from scratch" in r.stdout
+
+
+@pytest.mark.gpu
+def test_reference_memory_footprint_driver_on_gpu(cora, tmp_path):
+    exe = brc.OUT / "memory-footprint"
+    if not exe.exists():
+        pytest.skip("reference callers were not built where the snapshot was taken")
+    from dynamicgraphrepresentationlearning_b200 import graph_io
+    n, off, adj = cora
+    graph_io.write_unweighted_graph(tmp_path / "cora.adj", off, adj)
+    r = subprocess.run([str(exe), "-f", str(tmp_path / "cora.adj"), "-model", "node2vec", "-det", "false"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Walking model: NODE2VEC" in r.stdout and "Vertices: 2708, Edges: 10556" in r.stdout and "Device memory" in r.stdout

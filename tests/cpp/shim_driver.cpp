@@ -54,6 +54,17 @@ int main(int argc, char** argv_main)
         for (types::WalkID w = 0; w < (types::WalkID) n * config::walks_per_vertex; w++) std::printf("%s %llu: %s\n", tag, (unsigned long long) w, wharf.walk(w).c_str());
     };
     dump("initial");
+    {
+        auto tree = wharf.flatten_vertex_tree();                // wharfmh.h:140, read the way tests/wharfmh.cpp:65-99 reads it
+        size_t entries = 0, mapped = 0;
+        for (size_t v = 0; v < tree.size(); v++) entries += tree[v].inverted_index.size();
+        wharf.map_vertices([&](const auto& entry, size_t i) { mapped += entry.first == i && entry.second.compressed_edges.degree() == tree[i].compressed_edges.size(); });
+        uintV* row = tree[2].compressed_edges.get_edges(2);
+        std::printf("vertex tree %zu vertices %zu index entries, vertex 2: degree %zu first %u last %u index %zu root %d samplers %zu mapped %zu\n", tree.size(), entries,
+                    tree[2].compressed_edges.degree(), row[0], row[4], tree[2].inverted_index.size(), tree[2].inverted_index.root != nullptr,
+                    tree[2].sampler_manager->size(), mapped);
+        pbbs::free_array(row);
+    }
     std::printf("vertex_at_walk(2,3) = %u\n", (unsigned) wharf.vertex_at_walk(2, 3));
 
     auto* batch = pbbs::new_array_no_init<std::tuple<uintV, uintV>>(2);

@@ -46,6 +46,8 @@ def test_cpp_shim_reproduces_reference_corpora(tmp_path):
     for tag, walks in zip(("initial", "inserted", "deleted"), six["walks"]):
         got = [l.split(": ", 1)[1] for l in out if l.startswith(tag + " ")]
         assert got == ["".join(f"{v} " for v in w) for w in walks], tag     # WharfMH::walk format, wharfmh.h:376
+    twos = sum(w.count(2) for w in six["walks"][0])
+    assert f"vertex tree 6 vertices 96 index entries, vertex 2: degree 5 first 0 last 5 index {twos} root 1 samplers 0 mapped 6" in out   # flatten_vertex_tree / map_vertices
     assert "vertex_at_walk(2,3) = 3" in out
     assert "insert affected 12 first (0,3) edges 20" in out                  # caller's batch sorted in place (:452)
     assert "delete affected 12 edges 18" in out

@@ -93,6 +93,9 @@ SIGNATURES = {
     "wmh_global_to_local_walk": (C.c_int64, [vp, u64]),
     "wmh_walk_owner": (u32, [vp, u64]),
     "wmh_local_walk_ids": (u64, [vp, vp, u64]),
+    "wmh_random_stream": (None, [u64, u64, vp]),
+    "wmh_unit_double": (C.c_double, [u64]),
+    "wmh_keyed_draw": (u64, [u64, u64, u64, u64, u64]),
     "wmh_partition_owner": (u32, [u64, u32, u32, u64]),
     "wmh_partition_local_walk_ids": (u64, [u64, u32, u32, u32, vp, u64]),
     "wmh_parse_adjacency_graph": (i32, [vp, u64, PU64, PU64, vp, vp]),

@@ -970,6 +970,19 @@ uint32_t wmh_walk_owner(const wmh_engine* e, uint64_t walk_id)
     return (e->have_walks ? e->map : config_map(*e)).owner(walk_id);
 }
 
+// ---- the generators, host forms (no device needed): the very functions the draw table and the kernels are built from ----
+void wmh_random_stream(uint64_t seed, uint64_t count, uint64_t* out)
+{
+    if (!out) return;
+    u64 s[2];
+    random_seed(seed, s);
+    for (u64 k = 0; k < count; k++) out[k] = random_next(s);
+}
+
+double wmh_unit_double(uint64_t draw) { return unit_double(draw); }
+
+uint64_t wmh_keyed_draw(uint64_t seed, uint64_t domain, uint64_t a, uint64_t b, uint64_t c) { return keyed_draw(seed, domain, a, b, c); }
+
 uint32_t wmh_partition_owner(uint64_t n, uint32_t walks_per_vertex, uint32_t world, uint64_t walk_id)
 {
     if (n == 0 || world == 0 || walks_per_vertex == 0) return 0;

@@ -345,6 +345,23 @@ def trim_memory(device: int = 0) -> None:
 
 # ---- pairings (walks/pairings.h) over torch / raw device pointers ------------------------------------
 
+def random_stream(seed: int, count: int) -> np.ndarray:
+    """The first `count` lrand() of utility::Random(seed) (utils/utility.h:152-206): row `seed` of the draw table."""
+    out = np.empty(count, dtype=np.uint64)
+    capi.load().wmh_random_stream(seed, count, _ptr(out))
+    return out
+
+
+def unit_double(draw: int) -> float:
+    """utility::Random::drand applied to one 64-bit draw (utils/utility.h:208-218)."""
+    return float(capi.load().wmh_unit_double(draw))
+
+
+def keyed_draw(seed: int, domain: int, a: int, b: int, c: int) -> int:
+    """The counter-based draw of keyed MH mode (include/wharfmh_b200.h, wmh_keyed_draw)."""
+    return int(capi.load().wmh_keyed_draw(seed, domain, a, b, c))
+
+
 def partition_owner(n: int, walks_per_vertex: int, world: int, walk_id: int) -> int:
     """Rank that owns a global walk id under the sharding rule of include/wharfmh_b200.h (host arithmetic, no device)."""
     return int(capi.load().wmh_partition_owner(int(n), int(walks_per_vertex), int(world), int(walk_id)))

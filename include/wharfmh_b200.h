@@ -300,6 +300,19 @@ WMH_API uint64_t wmh_peer_bytes_needed(const wmh_engine* e);
 /* Number of generate passes that used the peer exchange so far (0: every pass ran stand-alone). */
 WMH_API uint64_t wmh_peer_exchanges(const wmh_engine* e);
 
+/* ---- the generators, host scalar forms (no device needed) ------------------------------------------ */
+
+/* utility::Random(seed) followed by `count` lrand() calls (utils/utility.h:157-170 seeding with arithmetic
+ * shifts, :194-206 xoroshiro128+ 55/14/36).  Deterministic mode's draw table is row r = this stream for
+ * seed r (graph/wharfmh.h:289-291: one Random(walk_id / n) per walk). */
+WMH_API void wmh_random_stream(uint64_t seed, uint64_t count, uint64_t* out);
+/* utility::Random::drand applied to one 64-bit draw (utils/utility.h:208-218): [0, 1). */
+WMH_API double wmh_unit_double(uint64_t draw);
+/* The counter-based generator of keyed MH mode: the draw for (seed, domain, a, b, c); domain 1 = walk step
+ * (a = global walk id, b = position, c = draw number), 2 = node2vec initial state (a = walk id),
+ * 3 = sampler init (a = cur, b = prev << 32 | generation of cur's sampler manager, c = proposal number). */
+WMH_API uint64_t wmh_keyed_draw(uint64_t seed, uint64_t domain, uint64_t a, uint64_t b, uint64_t c);
+
 /* ---- synthetic input (utils/utility.h:55-146 generate_batch_of_edges, rmat_util.h) --------------- */
 
 /* Device restatement of utility::generate_batch_of_edges: RMAT(a,b,c) edges over 2^(log2_up(vertices)-1)

@@ -93,6 +93,30 @@ def test_partition_rule_on_the_host(wharf, n, world, wpv):
         assert set(shared.tolist()) == {0, 1, 2, 3} and len({int(shared[b * 4]) for b in range(100)}) > 1
 
 
+def test_generators_on_the_host(wharf, wo, golden):
+    """SURVEY 8a row a3 pinned on the PRODUCT's own host functions (the code the draw table and the kernels are built
+    from, csrc/rng.cuh), without a GPU: utility::Random's stream against the unmodified reference's values
+    (tests/golden/golden.json "random", "drand"), the keyed generator against the CPU restatement's."""
+    assert wharf.random_stream(0, 3).tolist() == [10407335079877134008, 3962074050977524353, 12330921719341810270]      # SURVEY 8c
+    assert wharf.random_stream(1, 3).tolist() == [7437716154062571297, 1116485288419732103, 9741853272534875990]
+    assert wharf.random_stream(2, 3).tolist() == [2528678525309737254, 8345201964650685463, 16366336586872171348]
+    for seed, values in golden["random"].items():
+        assert wharf.random_stream(int(seed), len(values)).tolist() == values
+    for seed, values in golden["drand"].items():                        # drand = unit_double(lrand()), utils/utility.h:208-218
+        assert [wharf.unit_double(int(x)) for x in wharf.random_stream(int(seed), len(values))] == values
+    table = wo.draw_table(10, 80)                                       # deterministic mode's only randomness: X[r][k]
+    for r in range(10):
+        assert np.array_equal(wharf.random_stream(r, 80), table[r])
+    assert wharf.unit_double(0) == 0.0 and wharf.unit_double(2 ** 64 - 1) == 1.0 - 2.0 ** -52
+    rng = np.random.default_rng(11)
+    L = wo.lib()
+    for _ in range(2000):
+        seed, a, b, c = (int(x) for x in rng.integers(0, 2 ** 63, size=4, dtype=np.uint64) * 2 + rng.integers(0, 2, size=4, dtype=np.uint64))
+        dom = int(rng.integers(1, 4))
+        assert wharf.keyed_draw(seed, dom, a, b, c) == int(L.wo_keyed(seed, dom, a, b, c))
+    assert wharf.keyed_draw(1, 1, 0, 0, 0) != wharf.keyed_draw(1, 1, 0, 0, 1) != wharf.keyed_draw(1, 2, 0, 0, 0)
+
+
 def test_no_cpu_fallback(wharf):
     import torch
     if torch.cuda.is_available():

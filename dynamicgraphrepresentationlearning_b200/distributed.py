@@ -138,6 +138,21 @@ class ShardedWharfMH:
         dist.broadcast_object_list(box, src=owner, group=self.group)
         return box[0]
 
+    def write_walks(self, path, walk_ids, append: bool = False) -> int:
+        """The walks.txt hand-off (experiments/src/vertex-classification.cpp:167-178) of a sharded corpus: `walk_ids` are
+        global ids (what insert/delete_edges_batch returned, the same on every rank); every rank writes the walks it
+        owns, one rank after the other, into the same file - the ranks of a box share the file system, and no walk
+        crosses a link.  Lines come out grouped by rank, ascending id inside a group (the reference's order is its hash
+        map's).  Returns the bytes written by all ranks.  Collective."""
+        ids = np.asarray(walk_ids, dtype=np.uint64)
+        mine = ids[np.isin(ids, self.engine.local_walk_ids())]
+        written = 0
+        for turn in range(self.world):
+            if turn == self.rank:
+                written = self.engine.write_walks(path, np.sort(mine), append=append or turn > 0)
+            dist.barrier(group=self.group)
+        return self._all_reduce_sum(written)
+
     def local_walks(self) -> tuple[np.ndarray, np.ndarray]:
         """(global ids, rows) of the walks this rank owns."""
         return self.engine.local_walk_ids(), self.engine.walks()

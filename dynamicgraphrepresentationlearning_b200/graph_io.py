@@ -139,7 +139,4 @@ def format_walks(rows) -> bytes:
 def write_walks(engine: WharfMH, path, walk_ids, append: bool = False) -> int:
     """walks.txt (vertex-classification.cpp:167-178): the named walks (global ids this engine holds, e.g. what
     insert_edges_batch returned) gathered from the device and written as text.  Returns the bytes written."""
-    ids = np.ascontiguousarray(walk_ids, dtype=np.uint64)
-    written = C.c_uint64()
-    check(engine._lib.wmh_write_walks(engine._h, _ptr(ids), ids.shape[0], os.fspath(path).encode(), int(append), C.byref(written)))
-    return int(written.value)
+    return engine.write_walks(path, walk_ids, append=append)

@@ -230,6 +230,15 @@ class WharfMH:
         check(self._lib.wmh_walks_gather(self._h, _ptr(ids), ids.shape[0], _ptr(out)))
         return out
 
+    def write_walks(self, path, walk_ids, append: bool = False) -> int:
+        """walks.txt (experiments/src/vertex-classification.cpp:167-178): walk(id) + newline for every id (global ids
+        this engine holds), gathered from the device in bulk.  Returns the bytes written."""
+        import os
+        ids = np.ascontiguousarray(walk_ids, dtype=np.uint64)
+        written = C.c_uint64()
+        check(self._lib.wmh_write_walks(self._h, _ptr(ids), ids.shape[0], os.fspath(path).encode(), int(append), C.byref(written)))
+        return int(written.value)
+
     def local_to_global_walk(self, local: int) -> int:
         return int(self._lib.wmh_local_to_global_walk(self._h, local))
 

@@ -61,6 +61,15 @@ class OracleShard:
         row = self.o.walks()[walk_id]
         return "".join(f"{v} " for v in row[row != 0xFFFFFFFF])
 
+    def write_walks(self, path, walk_ids, append=False):
+        from dynamicgraphrepresentationlearning_b200 import graph_io
+        ids = np.asarray(walk_ids, dtype=np.int64)
+        assert np.isin(ids, self.local_walk_ids()).all()               # the engine refuses walks it does not hold
+        text = graph_io.format_walks(self.o.walks()[ids])
+        with open(path, "ab" if append else "wb") as f:
+            f.write(text)
+        return len(text)
+
     def destroy(self):
         self.o.close()
 
@@ -90,6 +99,20 @@ def _worker(rank, world, port, out_dir):
             gids, rows = sharded.local_walks()
             ok &= np.array_equal(rows, single.walks()[gids.astype(np.int64)])
             ok &= all(sharded.engine.walk_owner(int(g)) == rank for g in gids[::7])
+        # walks.txt of the last batch's affected walks: one file, every rank writes its own share in turn
+        from dynamicgraphrepresentationlearning_b200 import graph_io, partition_owner
+        path = Path(out_dir) / "walks.txt"
+        if rank == 0:
+            path.write_text("stale\n")
+        dist.barrier()
+        total = sharded.write_walks(path, ids)
+        order = sorted((int(w) for w in ids), key=lambda w: (partition_owner(n, 3, world, w), w))
+        want = graph_io.format_walks(single.walks()[np.array(order, dtype=np.int64)])
+        ok &= total == len(want) and path.read_bytes() == want
+        dist.barrier()                                                   # every rank has read the file before it grows
+        ok &= sharded.write_walks(path, ids[:5], append=True) > 0
+        ok &= path.read_bytes().startswith(want) and path.read_bytes().count(b"\n") == len(order) + 5
+        dist.barrier()
         ok &= sharded.walk(5) == sharded.walk(5) and sharded.walk(258).startswith("2 ")
         empty = sharded.insert_edges_batch(np.empty((0, 2), dtype=np.uint32) if rank == 0 else None)
         ok &= empty.shape[0] == 0

@@ -196,3 +196,55 @@ def test_stream_ingest_and_walks_txt(wharf, gio, golden, cora, cora_pairs, wo, t
         assert gio.write_walks(e, tmp_path / "shard.txt", mine[:5]) > 0
         with pytest.raises(wharf.WharfError, match="not held"):
             gio.write_walks(e, tmp_path / "shard.txt", np.array([0], dtype=np.uint64))
+
+
+# ---- a second real graph: experiments/data/wiki-graph (1996 of its 17981 lines are self-loops, 42 vertices end up isolated) ----
+@pytest.fixture(scope="module")
+def wiki():
+    gold = json.loads((GOLDEN_DIR / "wiki_golden.json").read_text())
+    z = np.load(GOLDEN_DIR / "wiki_graph.npz")
+    return gold, np.load(GOLDEN_DIR / "wiki_edge_list.npz")["pairs"], z["offsets"], z["edges"]
+
+
+def sha(a) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_wiki_text_and_oracle_follow_the_reference(gio, wo, wiki):
+    gold, pairs, off, adj = wiki
+    n = gold["n"]
+    assert (n, adj.shape[0], pairs.shape[0], int((pairs[:, 0] == pairs[:, 1]).sum())) == (2405, gold["m"], gold["lines"], gold["self_loops"])
+    assert hashlib.sha256(gio.format_unweighted_graph(off, adj)).hexdigest() == gold["adj_sha256"]          # SNAPtoAdj -s's file
+    got, vertices = gio.read_edge_list("".join(f"{u}\t{v}\n" for u, v in pairs.tolist()).encode())         # the file is tab-separated
+    assert vertices == n and np.array_equal(got, pairs)
+    # the CPU restatement against the unmodified reference's corpora on this graph (isolated starts included)
+    o = wo.Oracle(n, off, adj)
+    assert o.generate() == gold["phases"][0]["steps"] == 80 * 10 * int((np.diff(np.append(off, np.uint64(adj.shape[0])).astype(np.int64)) > 0).sum())
+    assert o.walks()[0, :10].tolist() == gold["walk0_prefix"]
+    assert sha(o.walks()) == gold["phases"][0]["walks_sha256"]
+    for (kind, size, seed), ph in zip(gold["ops"], gold["phases"][1:]):
+        b = wo.generate_batch(size, n, seed, False, False)
+        assert o.update(b, delete=kind == "del", remove_dups=True) == ph["affected"]
+        assert o.m == ph["m"] and sha(o.affected()[0]) == ph["affected_sha256"] and sha(o.walks()) == ph["walks_sha256"]
+    o.close()
+
+
+@pytest.mark.gpu
+def test_wiki_ingest_and_corpora_on_gpu(wharf, gio, wo, wiki):
+    gold, pairs, off, adj = wiki
+    n = gold["n"]
+    got_n, got_m, got_off, got_adj = gio.snap_to_adj(pairs)                         # loops and duplicates dropped on the device
+    assert (got_n, got_m) == (n, gold["m"]) and np.array_equal(got_off, off) and np.array_equal(got_adj, adj)
+    cfg = wharf.Config(walks_per_vertex=10, walk_length=80, random_walk_model=wharf.DEEPWALK, deterministic_mode=True)
+    for mode in (wharf.SEARCH_SCAN, wharf.SEARCH_INDEX):
+        cfg.search_mode = mode
+        with gio.graph_from_edge_list(pairs, config=cfg) as e:                      # straight from the edge list
+            assert e.generate_initial_random_walks() == gold["phases"][0]["steps"]
+            assert sha(e.walks()) == gold["phases"][0]["walks_sha256"]
+            assert fnv1a(gio.format_walks(e.walks()[:500])) == fnv1a("".join(e.walk(w) + "\n" for w in range(500)).encode())
+            for (kind, size, seed), ph in zip(gold["ops"], gold["phases"][1:]):
+                b = wo.generate_batch(size, n, seed, False, False)
+                fn = e.delete_edges_batch if kind == "del" else e.insert_edges_batch
+                affected = fn(b.copy(), sorted=False, remove_dups=True, nn=4096)
+                assert affected.shape[0] == ph["affected"] and e.number_of_edges() == ph["m"]
+                assert sha(affected) == ph["affected_sha256"] and sha(e.walks()) == ph["walks_sha256"]

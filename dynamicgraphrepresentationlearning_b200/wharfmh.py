@@ -354,6 +354,18 @@ def trim_memory(device: int = 0) -> None:
 
 # ---- pairings (walks/pairings.h) over torch / raw device pointers ------------------------------------
 
+def generate_batch_of_edges(edges_number: int, vertices_number: int, batch_seed: int, self_loops: bool = False, directed: bool = True,
+                            a: float = 0.5, b: float = 0.2, c: float = 0.1, device: int = 0) -> np.ndarray:
+    """utility::generate_batch_of_edges (utils/utility.h:55-146), produced on the device: (k, 2) uint32 pairs sorted by
+    (src, dst), duplicates (and, unless self_loops, loops) removed - the same bytes the reference's generator returns."""
+    slots = edges_number * (1 if directed else 2)
+    out = np.empty((slots, 2), dtype=np.uint32)
+    k = C.c_uint64()
+    check(capi.load().wmh_generate_batch_of_edges(device, edges_number, vertices_number, batch_seed, int(self_loops), int(directed), a, b, c,
+                                                  _ptr(out), slots, C.byref(k)))
+    return out[: int(k.value)].copy()
+
+
 def random_stream(seed: int, count: int) -> np.ndarray:
     """The first `count` lrand() of utility::Random(seed) (utils/utility.h:152-206): row `seed` of the draw table."""
     out = np.empty(count, dtype=np.uint64)

@@ -248,3 +248,16 @@ def test_wiki_ingest_and_corpora_on_gpu(wharf, gio, wo, wiki):
                 affected = fn(b.copy(), sorted=False, remove_dups=True, nn=4096)
                 assert affected.shape[0] == ph["affected"] and e.number_of_edges() == ph["m"]
                 assert sha(affected) == ph["affected_sha256"] and sha(e.walks()) == ph["walks_sha256"]
+
+
+@pytest.mark.gpu
+def test_generate_batch_of_edges_equals_the_reference_generator(wharf, golden):
+    """utility::generate_batch_of_edges through the host-facing entry point (what throughput-latency.cpp:121 calls):
+    byte-identical to the unmodified reference's batches (tests/golden/golden.json "genbatch")."""
+    for g in golden["genbatch"]:
+        b = wharf.generate_batch_of_edges(g["edges"], g["vertices"], g["seed"], bool(g["self_loops"]), bool(g["directed"]))
+        assert b.dtype == np.uint32 and b.shape == (g["count"], 2)
+        assert b[0].tolist() == g["first"] and b[-1].tolist() == g["last"]
+        assert hashlib.sha256(b.tobytes()).hexdigest() == g["sha256"]
+    with pytest.raises(wharf.WharfError):
+        wharf.generate_batch_of_edges(10, 1, 0)                       # fewer than two vertices

@@ -205,8 +205,8 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
         struct Samplers                                                  // graph/vertex.h:12 SamplerManager
         {
             bool untouched = true;
-            // Exact while no Metropolis-Hastings walk can have run (deterministic mode).  Afterwards the states live in
-            // the aux words of the device rows, keyed by edge, and are not counted per vertex.
+            // Exact while no Metropolis-Hastings walk has run on the engine (deterministic mode never touches a sampler).
+            // Afterwards the states live in the aux words of the device rows, keyed by edge, and are not counted per vertex.
             size_t size() const
             {
                 if (!untouched) throw std::logic_error("wharfmh_b200: sampler states are kept per edge on the device, not per vertex");
@@ -270,7 +270,7 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
 
         WharfMH(const WharfMH&) = delete;
         WharfMH& operator=(const WharfMH&) = delete;
-        WharfMH(WharfMH&& o) noexcept : engine_(o.engine_) { o.engine_ = nullptr; }
+        WharfMH(WharfMH&& o) noexcept : engine_(o.engine_), mh_walked_(o.mh_walked_) { o.engine_ = nullptr; }
         ~WharfMH() { destroy(); }
 
         [[nodiscard]] size_t number_of_vertices() const { return wmh_number_of_vertices(engine_); }   // :117
@@ -293,7 +293,7 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
             std::vector<uint64_t> index_sizes(n);
             detail::check(wmh_flatten_graph(engine_, row_ptr.data(), col.data()));
             detail::check(wmh_index_sizes(engine_, index_sizes.data()));
-            return FlatVertexTree(std::move(row_ptr), std::move(col), index_sizes, config::deterministic_mode);
+            return FlatVertexTree(std::move(row_ptr), std::move(col), index_sizes, !mh_walked_);
         }
 
         // :219.  map_function(entry, i) with entry.first = the vertex and entry.second = its entry, in vertex order.
@@ -404,6 +404,7 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
 
     private:
         wmh_engine* engine_ = nullptr;
+        bool mh_walked_ = false;             // a generate or batch ran with deterministic_mode off: sampler states may exist
 
         void sync_config()
         {
@@ -411,6 +412,7 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
             detail::check(wmh_get_config(engine_, &cur));
             want.rank = cur.rank; want.world = cur.world; want.device = cur.device;
             detail::check(wmh_set_config(engine_, &want));
+            if (!config::deterministic_mode) mh_walked_ = true;      // called by every member that can walk
         }
 
         pbbs::sequence<types::WalkID> batch(bool is_delete, size_t m, std::tuple<uintV, uintV>* edges, bool sorted, bool remove_dups, size_t nn,

@@ -140,3 +140,24 @@ def write_walks(engine: WharfMH, path, walk_ids, append: bool = False) -> int:
     """walks.txt (vertex-classification.cpp:167-178): the named walks (global ids this engine holds, e.g. what
     insert_edges_batch returned) gathered from the device and written as text.  Returns the bytes written."""
     return engine.write_walks(path, walk_ids, append=append)
+
+
+def main(argv=None) -> int:
+    """`python -m dynamicgraphrepresentationlearning_b200.graph_io [-s] [-f] <edge list> <adjacency graph>`: the command
+    line of experiments/bin/SNAPtoAdj (-s symmetrises; -f is accepted and ignored as there), with the set work done on
+    the device."""
+    import sys
+    args = [a for a in (sys.argv[1:] if argv is None else argv)]
+    symmetric = "-s" in args
+    files = [a for a in args if a not in ("-s", "-f")]
+    if len(files) != 2:
+        print("usage: graph_io [-s] [-f] <SNAP edge list> <AdjacencyGraph output>", file=sys.stderr)
+        return 2
+    n, m, offsets, edges = snap_to_adj(files[0], symmetric=symmetric)
+    write_unweighted_graph(files[1], offsets, edges)
+    print(f"Vertices: {n} Edges: {m}")
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

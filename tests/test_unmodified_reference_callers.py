@@ -8,8 +8,9 @@ libwharfmh_b200.so - no line of them is edited or copied; they are compiled wher
 
   * here (no GPU): all four experiments/src drivers and tests/wharfmh.cpp compile and link; tests/pairings.cpp also RUNS -
     its known-answer and 10 M round-trip tests pass against the library's pairing functions;
-  * on the B200: the reference's throughput-latency driver runs on cora and the affected-walk counts it prints equal the
-    CPU oracle's replay of the same batch sequence; memory-footprint runs to completion.
+  * on the B200: the reference's throughput-latency driver runs on cora and the batch sizes and affected-walk counts it
+    prints equal what the same source prints when built with the reference's own headers
+    (tests/golden/driver_golden.json) and the CPU oracle's replay of the sequence; memory-footprint runs to completion.
 googletest is not installed: tests/cpp/mini_gtest/ is a 60-line runner with its spelling (test infrastructure)."""
 import re
 import subprocess
@@ -65,6 +66,36 @@ def test_drivers_fail_loudly_without_gpu(tmp_path):
     assert r.returncode != 0 and "no CPU path" in r.stderr              # ... the engine refused to
 
 
+def replay_throughput_latency(wo, n, off, adj):
+    """The driver's sequence on the CPU oracle: generate, then per batch size (throughput-latency.cpp:87-90) an insert and a
+    delete of generate_batch_of_edges(size, n, 0, false, true)."""
+    o = wo.Oracle(n, off, adj, walks_per_vertex=10, walk_length=80)
+    o.generate()
+    counts, sizes = [], []
+    for size in (5, 50, 500):
+        b = wo.generate_batch(size, n, 0, False, True)
+        sizes.append(int(b.shape[0]))
+        for delete in (False, True):
+            o.update(b.copy(), delete=delete, remove_dups=True)
+            counts.append(float(o.affected()[0].shape[0]))
+    o.close()
+    return sizes, counts
+
+
+def driver_golden():
+    import json
+    return json.loads((ROOT / "tests" / "golden" / "driver_golden.json").read_text())
+
+
+def test_oracle_replays_what_the_reference_driver_prints(wo, cora):
+    """tests/golden/driver_golden.json = the output of the reference's driver built with the reference's own headers
+    (tests/golden/make_driver_golden.py): directed batches, inserts and deletes, affected-walk counts."""
+    gold = driver_golden()
+    sizes, counts = replay_throughput_latency(wo, *cora)
+    assert sizes == gold["batch_pairs"] == [5, 50, 490]
+    assert counts == gold["walks_affected"]
+
+
 @pytest.mark.gpu
 def test_reference_throughput_latency_driver_on_gpu(wharf, wo, cora, tmp_path):
     exe = brc.OUT / "throughput-latency"
@@ -78,19 +109,10 @@ def test_reference_throughput_latency_driver_on_gpu(wharf, wo, cora, tmp_path):
     assert "Walking model: DEEPWALK" in r.stdout and "Vertices: 2708 Edges: 10556" in r.stdout
     got = [float(x) for x in re.findall(r"Average number of walks affected = ([0-9.e+]+)", r.stdout)]
     batch_sizes = [int(x) for x in re.findall(r"Batch size = \d+ \| (\d+) ", r.stdout)]
-    # the same sequence on the CPU oracle: generate, then per batch size insert + delete of generate_batch_of_edges(size, n, 0, false, true)
-    o = wo.Oracle(n, off, adj, walks_per_vertex=10, walk_length=80)
-    o.generate()
-    want, sizes = [], []
-    for size in (5, 50, 500):                                           # throughput-latency.cpp:87-90
-        b = wo.generate_batch(size, n, 0, False, True)
-        sizes.append(b.shape[0])
-        for delete in (False, True):
-            o.update(b.copy(), delete=delete, remove_dups=True)
-            want.append(float(o.affected()[0].shape[0]))
-    o.close()
-    assert batch_sizes == sizes
-    assert got == want
+    sizes, want = replay_throughput_latency(wo, n, off, adj)
+    gold = driver_golden()                                             # the same source built with the reference's own headers
+    assert batch_sizes == sizes == gold["batch_pairs"]
+    assert got == want == gold["walks_affected"]
     assert "Average time to generate random walks from scratch" in r.stdout
 
 

@@ -261,3 +261,42 @@ def test_generate_batch_of_edges_equals_the_reference_generator(wharf, golden):
         assert hashlib.sha256(b.tobytes()).hexdigest() == g["sha256"]
     with pytest.raises(wharf.WharfError):
         wharf.generate_batch_of_edges(10, 1, 0)                       # fewer than two vertices
+
+
+# ---- the incremental flow of vertex-classification.cpp:118-197: vertices in isolation, then the edge stream ----------
+@pytest.fixture(scope="module")
+def stream_golden():
+    return json.loads((GOLDEN_DIR / "stream_golden.json").read_text())
+
+
+def test_edge_stream_from_empty_graph_oracle(gio, wo, stream_golden, cora_pairs):
+    g = stream_golden
+    n = g["n"]
+    o = wo.Oracle(n, np.zeros(n, dtype=np.uint64), np.zeros(0, dtype=np.uint32))
+    assert o.generate() == g["phases"][0]["steps"] == 0                # every walk is its start vertex alone
+    assert sha(o.walks()) == g["phases"][0]["walks_sha256"]
+    stream = gio.create_edge_stream(cora_pairs, g["partition"])
+    assert len(stream) == len(g["phases"]) - 1
+    for batch, ph in zip(stream, g["phases"][1:]):
+        assert o.update(batch.copy(), delete=False, remove_dups=True) == ph["affected"]
+        assert o.m == ph["m"] and sha(o.affected()[0]) == ph["affected_sha256"] and sha(o.walks()) == ph["walks_sha256"]
+    o.close()
+
+
+@pytest.mark.gpu
+def test_edge_stream_from_empty_graph_on_gpu(wharf, gio, stream_golden, cora, cora_pairs, tmp_path):
+    g = stream_golden
+    n, off, adj = cora
+    cfg = wharf.Config(walks_per_vertex=10, walk_length=80, random_walk_model=wharf.DEEPWALK, deterministic_mode=True)
+    with wharf.WharfMH(n, config=cfg) as e:                              # WharfMH(n, m): all vertices in isolation (wharfmh.h:26)
+        assert e.generate_initial_random_walks() == 0
+        assert sha(e.walks()) == g["phases"][0]["walks_sha256"]
+        assert gio.format_walks(e.walks()[:3]) == b"0 \n1 \n2 \n"
+        for batch, ph in zip(gio.create_edge_stream(cora_pairs, g["partition"]), g["phases"][1:]):
+            affected = e.insert_edges_batch(batch, sorted=False, remove_dups=True)     # vertex-classification.cpp:170
+            assert affected.shape[0] == ph["affected"] and e.number_of_edges() == ph["m"]
+            assert sha(affected) == ph["affected_sha256"] and sha(e.walks()) == ph["walks_sha256"]
+            e.write_walks(tmp_path / "walks.txt", affected)                            # :172-178
+            assert fnv1a((tmp_path / "walks.txt").read_bytes()[:4096]) == fnv1a(gio.format_walks(e.walks_gather(affected[:200].astype(np.uint32)))[:4096])
+        rp, col = e.flatten_graph()
+        assert np.array_equal(rp[:-1], off) and np.array_equal(col, adj)                # the stream rebuilt SNAPtoAdj -s's graph

@@ -54,17 +54,6 @@ int main(int argc, char** argv_main)
         for (types::WalkID w = 0; w < (types::WalkID) n * config::walks_per_vertex; w++) std::printf("%s %llu: %s\n", tag, (unsigned long long) w, wharf.walk(w).c_str());
     };
     dump("initial");
-    {
-        auto tree = wharf.flatten_vertex_tree();                // wharfmh.h:140, read the way tests/wharfmh.cpp:65-99 reads it
-        size_t entries = 0, mapped = 0;
-        for (size_t v = 0; v < tree.size(); v++) entries += tree[v].inverted_index.size();
-        wharf.map_vertices([&](const auto& entry, size_t i) { mapped += entry.first == i && entry.second.compressed_edges.degree() == tree[i].compressed_edges.size(); });
-        uintV* row = tree[2].compressed_edges.get_edges(2);
-        std::printf("vertex tree %zu vertices %zu index entries, vertex 2: degree %zu first %u last %u index %zu root %d samplers %zu mapped %zu\n", tree.size(), entries,
-                    tree[2].compressed_edges.degree(), row[0], row[4], tree[2].inverted_index.size(), tree[2].inverted_index.root != nullptr,
-                    tree[2].sampler_manager->size(), mapped);
-        pbbs::free_array(row);
-    }
     std::printf("vertex_at_walk(2,3) = %u\n", (unsigned) wharf.vertex_at_walk(2, 3));
 
     auto* batch = pbbs::new_array_no_init<std::tuple<uintV, uintV>>(2);
@@ -77,18 +66,6 @@ int main(int argc, char** argv_main)
     std::printf("delete affected %zu edges %zu\n", affected.size(), wharf.number_of_edges());
     dump("deleted");
     pbbs::free_array(batch);
-
-    if (argc > 1)
-    {
-        const std::string walks_path = std::string(argv_main[1]) + "/walks.txt";
-        const size_t bytes = wharf.write_walks(walks_path.c_str(), affected);                // vertex-classification.cpp:167-178
-        std::ifstream f(walks_path);
-        std::string line;
-        size_t lines = 0;
-        bool same = true;
-        while (std::getline(f, line)) same = same && line == wharf.walk(affected[lines++]);
-        std::printf("walks.txt %zu bytes %zu lines same %d\n", bytes, lines, (int) same);
-    }
 
     auto flat = wharf.flatten_graph();
     std::printf("degree(2) = %zu\n", (size_t) flat[2].degree);

@@ -12,7 +12,9 @@
 #include <cerrno>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace wharf;
@@ -50,6 +52,39 @@ inline char* put_u64(char* out, u64 v, char tail)
     while (k) *out++ = tmp[--k];
     *out++ = tail;
     return out;
+}
+
+inline u64 digits_of_u32(u32 v)
+{
+    return v < 100000u ? (v < 100u ? (v < 10u ? 1 : 2) : (v < 10000u ? (v < 1000u ? 3 : 4) : 5))
+                       : (v < 10000000u ? (v < 1000000u ? 6 : 7) : (v < 1000000000u ? (v < 100000000u ? 8 : 9) : 10));
+}
+
+// Decimal digits of a 32-bit value followed by `tail`: the digit count is known first, so the digits go straight to
+// their places, two at a time.
+inline char* put_u32(char* out, u32 v, char tail)
+{
+    static const char kPairs[] = "0001020304050607080910111213141516171819202122232425262728293031323334353637383940414243444546474849"
+                                 "5051525354555657585960616263646566676869707172737475767778798081828384858687888990919293949596979899";
+    const u64 d = digits_of_u32(v);
+    char* q = out + d;
+    while (v >= 100)
+    {
+        const u32 r = v % 100;
+        v /= 100;
+        q -= 2;
+        q[0] = kPairs[2 * r];
+        q[1] = kPairs[2 * r + 1];
+    }
+    if (v >= 10)
+    {
+        q -= 2;
+        q[0] = kPairs[2 * v];
+        q[1] = kPairs[2 * v + 1];
+    }
+    else *--q = static_cast<char>('0' + v);
+    out[d] = tail;
+    return out + d + 1;
 }
 
 inline u64 digits_of(u64 v)
@@ -179,24 +214,48 @@ int wmh_parse_edge_list(const char* text, uint64_t bytes, uint32_t* pairs, uint6
 }
 
 // The text WharfMH::walk returns (graph/wharfmh.h:365-394: every vertex followed by one space), one walk per line.
+// Large corpora are formatted by several host threads: the walks are cut into contiguous segments, every segment is
+// sized, then written at its offset.
 uint64_t wmh_format_walks(const uint32_t* rows, uint64_t count, uint32_t walk_length, char* out, uint64_t capacity)
 {
     if (count && !rows) return 0;
-    u64 need = 0;
-    for (u64 w = 0; w < count; w++)
-    {
-        const u32* row = rows + w * walk_length;
-        for (u32 p = 0; p < walk_length && row[p] != WMH_NO_VERTEX; p++) need += digits_of(row[p]) + 1;
-        need += 1;
-    }
+    const u64 kWalksPerThread = 8192;
+    unsigned hw = std::thread::hardware_concurrency();
+    if (hw == 0) hw = 1;
+    const u64 parts = std::max<u64>(1, std::min<u64>({(u64) hw, 16, count / kWalksPerThread}));
+    std::vector<u64> begin(parts + 1), bytes(parts + 1, 0);
+    for (u64 s = 0; s <= parts; s++) begin[s] = count / parts * s + std::min<u64>(s, count % parts);
+    auto size_of = [&](u64 s) {
+        u64 need = 0;
+        for (u64 w = begin[s]; w < begin[s + 1]; w++)
+        {
+            const u32* row = rows + w * walk_length;
+            for (u32 p = 0; p < walk_length && row[p] != WMH_NO_VERTEX; p++) need += digits_of_u32(row[p]) + 1;
+            need += 1;
+        }
+        bytes[s + 1] = need;
+    };
+    auto write_of = [&](u64 s) {
+        char* q = out + bytes[s];
+        for (u64 w = begin[s]; w < begin[s + 1]; w++)
+        {
+            const u32* row = rows + w * walk_length;
+            for (u32 p = 0; p < walk_length && row[p] != WMH_NO_VERTEX; p++) q = put_u32(q, row[p], ' ');
+            *q++ = '\n';
+        }
+    };
+    auto run = [&](auto&& job) {
+        if (parts == 1) { job(0); return; }
+        std::vector<std::thread> pool;
+        for (u64 s = 1; s < parts; s++) pool.emplace_back([&job, s] { job(s); });
+        job(0);
+        for (auto& t : pool) t.join();
+    };
+    run(size_of);
+    for (u64 s = 0; s < parts; s++) bytes[s + 1] += bytes[s];      // -> offsets
+    const u64 need = bytes[parts];
     if (!out || capacity < need) return need;
-    char* q = out;
-    for (u64 w = 0; w < count; w++)
-    {
-        const u32* row = rows + w * walk_length;
-        for (u32 p = 0; p < walk_length && row[p] != WMH_NO_VERTEX; p++) q = put_u64(q, row[p], ' ');
-        *q++ = '\n';
-    }
+    run(write_of);
     return need;
 }
 

@@ -131,9 +131,9 @@ def format_walks(rows) -> bytes:
     if rows.ndim != 2:
         raise ValueError("rows must be [walks, walk_length]")
     need = lib.wmh_format_walks(_ptr(rows), rows.shape[0], rows.shape[1], None, 0)
-    buf = C.create_string_buffer(need)
-    lib.wmh_format_walks(_ptr(rows), rows.shape[0], rows.shape[1], buf, need)
-    return buf.raw
+    buf = np.empty(need, dtype=np.uint8)
+    lib.wmh_format_walks(_ptr(rows), rows.shape[0], rows.shape[1], _ptr(buf), need)
+    return buf.tobytes()
 
 
 def write_walks(engine: WharfMH, path, walk_ids, append: bool = False) -> int:

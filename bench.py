@@ -377,6 +377,11 @@ def main():
                                   "note": "fetch rate = ncu DRAM bytes read / 64 B over the ncu duration of the walk kernel alone"}}
     if isinstance(traffic, dict):
         roofline["traffic"] = traffic["read"] + traffic["write"]
+    if not spec["det"] and spec["model"] == "node2vec":
+        roofline["note"] = ("achieved = SURVEY 8d's algorithmic bytes of a node2vec MH step (descriptors, candidate, sampler state, two binary "
+                            "searches of N(prev)) x steps / time; frac > 1 means the kernel moves fewer bytes than that algorithm: the per-edge "
+                            "filter answers most membership tests with one sector and half the sectors hit the L2 (traffic = measured DRAM "
+                            "bytes). The binding limit is the DRAM fetch rate: see random_gather")
 
     # ---- deterministic-mode figure beside an MH headline (reference default mode, bit-exact corpus) ----
     extra = {}

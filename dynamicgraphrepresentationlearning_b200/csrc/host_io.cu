@@ -120,6 +120,10 @@ int wmh_parse_adjacency_graph(const char* text, uint64_t bytes, uint64_t* n_out,
     if (!parse_u64(p, end, n)) return report_failure(WMH_ERR_INVALID, "AdjacencyGraph: vertex count missing");
     skip();
     if (!parse_u64(p, end, m)) return report_failure(WMH_ERR_INVALID, "AdjacencyGraph: edge count missing");
+    // every further token takes at least two bytes: a header that promises more than the text can hold is refused
+    // before the caller sizes its arrays by it
+    if (n > bytes || m > bytes || 2 * (n + m) > static_cast<u64>(end - p) + 1)
+        return report_failure(WMH_ERR_INVALID, "Bad input file: fewer than n + m + 3 tokens (IO.h:94)");
     *n_out = n;
     *m_out = m;
     if (!offsets && !edges) return WMH_OK;                      // sizes only

@@ -300,3 +300,60 @@ def test_edge_stream_from_empty_graph_on_gpu(wharf, gio, stream_golden, cora, co
             assert fnv1a((tmp_path / "walks.txt").read_bytes()[:4096]) == fnv1a(gio.format_walks(e.walks_gather(affected[:200].astype(np.uint32)))[:4096])
         rp, col = e.flatten_graph()
         assert np.array_equal(rp[:-1], off) and np.array_equal(col, adj)                # the stream rebuilt SNAPtoAdj -s's graph
+
+
+# ---- differential fuzz of the text parsers against a line-by-line Python restatement ------------------------------------
+def py_edge_list(text: bytes):
+    """What wmh_parse_edge_list accepts: per line (split at \\n) - blank or first non-blank char # / % -> skipped; else exactly two
+    unsigned decimals < 2^32 - 2 separated by blanks.  Returns the pairs or None when any line is malformed."""
+    pairs = []
+    for line in text.split(b"\n"):
+        body = line.strip(b" \t\r\f\v")
+        if not body or body[:1] in (b"#", b"%"):
+            continue
+        tok = body.split()
+        if len(tok) != 2 or not all(t.isdigit() for t in tok):
+            return None
+        a, b = int(tok[0]), int(tok[1])
+        if a >= 2 ** 64 or b >= 2 ** 64 or a >= 0xFFFFFFFE or b >= 0xFFFFFFFE:
+            return None
+        pairs.append([a, b])
+    return pairs
+
+
+def test_edge_list_parser_differential_fuzz(wharf, gio):
+    rng = np.random.default_rng(2024)
+    alphabet = np.frombuffer(b"0123456789  \t\n\n\r#%x-", dtype=np.uint8)
+    agree = {"ok": 0, "bad": 0}
+    for trial in range(4000):
+        text = rng.choice(alphabet, size=int(rng.integers(0, 40))).tobytes()
+        if trial % 3 == 0:                                              # mostly well-formed files with one flaw somewhere
+            lines = [f"{rng.integers(0, 10 ** int(rng.integers(1, 11)))}{' ' * int(rng.integers(1, 3))}{rng.integers(0, 5000)}" for _ in range(int(rng.integers(0, 6)))]
+            text = ("\n".join(lines) + ("\n" if rng.random() < 0.5 else "")).encode() + (text if rng.random() < 0.3 else b"")
+        want = py_edge_list(text)
+        try:
+            got, vertices = gio.read_edge_list(text)
+        except wharf.WharfError:
+            assert want is None, text
+            agree["bad"] += 1
+            continue
+        assert want is not None and got.tolist() == want, text
+        assert vertices == (max(max(p) for p in want) + 1 if want else 0)
+        agree["ok"] += 1
+    assert agree["ok"] > 300 and agree["bad"] > 300
+
+
+def test_adjacency_parser_fuzz_never_reads_past_the_text(wharf, gio):
+    rng = np.random.default_rng(7)
+    base = b"AdjacencyGraph\n3\n4\n0\n2\n3\n1\n2\n0\n0\n"
+    assert gio.read_unweighted_graph(base)[:2] == (3, 4)
+    for _ in range(3000):
+        cut = base[: int(rng.integers(0, len(base) + 1))]
+        noise = bytes(rng.choice(np.frombuffer(b"0123456789 \n9x", dtype=np.uint8), size=int(rng.integers(0, 6))))
+        text = cut + noise if rng.random() < 0.5 else cut[: len(cut) // 2] + noise + cut[len(cut) // 2:]
+        try:
+            n, m, off, adj = gio.read_unweighted_graph(text)
+        except (wharf.WharfError, MemoryError, ValueError):
+            continue
+        tok = text.split()
+        assert tok[0] == b"AdjacencyGraph" and len(tok) == n + m + 3 and off.tolist() == [int(t) for t in tok[3:3 + n]] and adj.tolist() == [int(t) for t in tok[3 + n:]]

@@ -1,7 +1,7 @@
 # Random-gather rate against table footprint on one B200: where between 64 MiB (285 G loads/s, L2-resident) and 4 GiB
-# (37.7 G, the DRAM fetch-rate wall) the cliff lies.  The MH node2vec working set at scale-20 is 142 MB (descriptors +
-# interleaved rows); if ~100 MiB still gathers at L2 rate, a compact layout (u16 aux words apart from the neighbours,
-# 108 MB in all) would lift the headline configuration off the DRAM wall.
+# (37.7 G, the DRAM fetch-rate wall) the cliff lies.  The MH node2vec kernel's 50 % L2 hit rate on 134 MB of uniformly
+# accessed rows says the effective capacity for data every SM touches is ~67 MB (half the L2): this sweep measures it
+# directly.
 # usage (GPU box): bash tools/run_l2_footprint.sh <tag>
 set -x
 tag=${1:-l2}

@@ -377,6 +377,10 @@ def main():
                                   "note": "fetch rate = ncu DRAM bytes read / 64 B over the ncu duration of the walk kernel alone"}}
     if isinstance(traffic, dict):
         roofline["traffic"] = traffic["read"] + traffic["write"]
+    if spec["det"] and coalesced:
+        roofline["note"] = ("achieved = 68 B (SURVEY 8d: one descriptor sector + one neighbour sector + the stored vertex) x walker steps / time; "
+                            "frac > 1 because the coalesced schedule fetches a row once for every walker of a replica standing on it "
+                            "(walkers of one replica that meet are identical in deterministic mode): traffic = measured DRAM bytes")
     if not spec["det"] and spec["model"] == "node2vec":
         roofline["note"] = ("achieved = SURVEY 8d's algorithmic bytes of a node2vec MH step (descriptors, candidate, sampler state, two binary "
                             "searches of N(prev)) x steps / time; frac > 1 means the kernel moves fewer bytes than that algorithm: the per-edge "

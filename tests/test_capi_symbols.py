@@ -117,6 +117,25 @@ def test_generators_on_the_host(wharf, wo, golden):
     assert wharf.keyed_draw(1, 1, 0, 0, 0) != wharf.keyed_draw(1, 1, 0, 0, 1) != wharf.keyed_draw(1, 2, 0, 0, 0)
 
 
+def test_header_is_plain_c(tmp_path):
+    """The boundary is a C ABI: include/wharfmh_b200.h compiles as C99 (pedantic, warnings as errors) and a C program
+    links the library and calls host-only entry points."""
+    import subprocess
+    lib_dir = ROOT / "dynamicgraphrepresentationlearning_b200" / "lib"
+    src = tmp_path / "c_abi.c"
+    src.write_text('#include "wharfmh_b200.h"\n#include <stdio.h>\n'
+                   'int main(void) { wmh_config c; uint64_t x = 0, y = 0, s[2];\n'
+                   '  wmh_default_config(&c); wmh_szudzik_unpair(wmh_szudzik_pair(123, 25), &x, &y); wmh_random_stream(0, 2, s);\n'
+                   '  printf("%u %u %llu %llu %llu %u\\n", c.walks_per_vertex, c.walk_length, (unsigned long long) x, (unsigned long long) y,\n'
+                   '         (unsigned long long) s[0], wmh_partition_owner(100, 10, 2, 999));\n'
+                   '  return wmh_last_error() == 0; }\n')
+    exe = tmp_path / "c_abi"
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", f"-I{ROOT / 'include'}", str(src), "-o", str(exe),
+                    f"-L{lib_dir}", "-lwharfmh_b200", f"-Wl,-rpath,{lib_dir}"], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
+    assert out == ["10", "80", "123", "25", "10407335079877134008", "1"]       # config/globals.h defaults; pairing KAT; Random(0); replica 9 of 10 -> rank 1
+
+
 def test_no_cpu_fallback(wharf):
     import torch
     if torch.cuda.is_available():

@@ -30,6 +30,24 @@ def _compile(sources: list[Path], exe: Path, extra: list[str]) -> None:
     subprocess.run(cmd, check=True)
 
 
+# the reference's own graph/wharfmh.h and the C ABI in ONE translation unit (tests/cpp/intree_stub.cpp),
+# i.e. the unmodified reference engine and the B200 engine in one binary.  Flags of oracle/Makefile (-O2).
+REFERENCE_FLAGS = ["-DEDGELONG", "-mcx16", "-std=c++17", "-march=x86-64-v2", "-Wno-subobject-linkage", "-w", "-DUSEMALLOC", "-DHOMEGROWN", "-pthread", "-O2"]
+
+
+def build_intree_stub() -> Path:
+    exe = OUT / "intree_stub"
+    src = ROOT / "tests" / "cpp" / "intree_stub.cpp"
+    deps = [src, ROOT / "include" / "wharfmh_b200.h", LIB_DIR / "libwharfmh_b200.so", Path(__file__)]
+    if exe.exists() and all(exe.stat().st_mtime >= d.stat().st_mtime for d in deps if d.exists()):
+        return exe
+    OUT.mkdir(parents=True, exist_ok=True)
+    inc = [f"-I{REF / d}" for d in ("libs/libcuckoo", "libs/compressed_trees", "graph", "walks", "utils", "config")]
+    subprocess.run(["g++", *REFERENCE_FLAGS, *inc, f"-I{ROOT / 'include'}", str(src), "-o", str(exe), f"-L{LIB_DIR}", "-lwharfmh_b200",
+                    "-Wl,-rpath,$ORIGIN/../../../../dynamicgraphrepresentationlearning_b200/lib", "-ldl"], check=True)
+    return exe
+
+
 def build_all() -> list[Path]:
     if not reference_present():
         raise FileNotFoundError("/root/reference is not on this machine")
@@ -43,6 +61,7 @@ def build_all() -> list[Path]:
         exe = OUT / name
         _compile([REF / "tests" / src, MINI_GTEST / "main.cpp"], exe, [f"-I{MINI_GTEST}"])
         built.append(exe)
+    built.append(build_intree_stub())
     return built
 
 

@@ -31,7 +31,7 @@ needs_reference = pytest.mark.skipif(not brc.reference_present(), reason="/root/
 def test_reference_drivers_and_tests_compile_unchanged():
     built = brc.build_all()
     assert {p.name for p in built} == {"throughput-latency", "memory-throughput-latency", "memory-footprint", "vertex-classification",
-                                       "ref_test_wharfmh", "ref_test_pairings"}
+                                       "ref_test_wharfmh", "ref_test_pairings", "intree_stub"}
     assert all(p.exists() for p in built)
     # nothing of the reference was copied next to the binaries or into the compat headers
     assert not list((ROOT / "tests" / "cpp" / "_build" / "ref_callers").glob("*.cpp"))
@@ -64,6 +64,46 @@ def test_drivers_fail_loudly_without_gpu(tmp_path):
     r = subprocess.run([str(exe), "-f", str(tmp_path / "cora.adj")], capture_output=True, text=True)
     assert "Vertices: 2708 Edges: 10556" in r.stdout                    # the reader ran (host code) ...
     assert r.returncode != 0 and "no CPU path" in r.stderr              # ... the engine refused to
+
+
+def test_reference_and_library_in_one_binary_without_gpu(golden):
+    """tests/cpp/intree_stub.cpp = INTEGRATION.md section 2 made real: the reference's own graph/wharfmh.h and the C ABI in one
+    translation unit.  Without a GPU the reference half runs (its corpus equals the golden) and wmh_create refuses."""
+    exe = brc.OUT / "intree_stub"
+    if not exe.exists():
+        pytest.skip("reference callers not built on this machine")
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 3 and "no CPU path" in r.stderr
+    got = [l.split(": ", 1)[1] for l in r.stdout.splitlines() if l.startswith("reference ")]
+    assert got == ["".join(f"{v} " for v in w) for w in golden["six"]["walks"][0]]
+
+
+@pytest.mark.gpu
+def test_reference_and_library_side_by_side_on_gpu(golden, cora, tmp_path):
+    """The same binary on the B200: the UNMODIFIED reference (host threads) and the CUDA engine hold the same graph, take
+    the same insert and delete, and every walk of both is compared as text - first the six-vertex fixture, then cora
+    (27 080 walks, the reference's own generator for the batch)."""
+    exe = brc.OUT / "intree_stub"
+    if not exe.exists():
+        pytest.skip("reference callers were not built where the snapshot was taken")
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert "initial: 12 walks, differing 0, edges 18 / 18" in r.stdout
+    assert "inserted: affected 12 / 12" in r.stdout and "inserted: 12 walks, differing 0, edges 20 / 20" in r.stdout
+    assert "deleted: affected 12 / 12" in r.stdout and "deleted: 12 walks, differing 0, edges 18 / 18" in r.stdout
+    assert "total differing: 0" in r.stdout
+    from dynamicgraphrepresentationlearning_b200 import graph_io
+    n, off, adj = cora
+    graph_io.write_unweighted_graph(tmp_path / "cora.adj", off, adj)
+    r = subprocess.run([str(exe), str(tmp_path / "cora.adj"), "100"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    g = golden["cora"]["phases"]
+    assert f"initial: {10 * n} walks, differing 0, edges {g[0]['m']} / {g[0]['m']}" in r.stdout
+    assert f"inserted: affected {g[1]['affected']} / {g[1]['affected']}" in r.stdout and f"differing 0, edges {g[1]['m']} / {g[1]['m']}" in r.stdout
+    assert f"deleted: affected {g[2]['affected']} / {g[2]['affected']}" in r.stdout and "total differing: 0" in r.stdout
 
 
 def replay_throughput_latency(wo, n, off, adj):

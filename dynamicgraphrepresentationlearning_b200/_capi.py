@@ -83,6 +83,7 @@ SIGNATURES = {
     "wmh_delete_edges_batch_device": (i32, [vp, u64, vp, i32, i32, PU64]),
     "wmh_affected_walks": (i32, [vp, vp, vp, u64]),
     "wmh_affected_walks_device": (i32, [vp, C.POINTER(vp), C.POINTER(vp), PU64]),
+    "wmh_affected_walks_global_device": (i32, [vp, vp, u64]),
     "wmh_touched_vertices": (i32, [vp, vp, u64, PU64]),
     "wmh_walk": (i32, [vp, u64, vp, PU32]),
     "wmh_walk_string": (i32, [vp, u64, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
@@ -123,6 +124,8 @@ SIGNATURES = {
     "wmh_memory_footprint": (i32, [vp, C.POINTER(WmhMemory)]),
     "wmh_kernel_launches": (u64, [vp]),
     "wmh_last_walk_kernel_ms": (C.c_double, [vp]),
+    "wmh_last_index_ms": (C.c_double, [vp]),
+    "wmh_last_search_mode": (u32, [vp]),
     "wmh_device_walks": (vp, [vp]),
     "wmh_stream": (vp, [vp]),
     "wmh_synchronize": (i32, [vp]),

@@ -59,6 +59,11 @@ inline unsigned grid_for(u64 work_items, unsigned block, unsigned blocks_per_sm,
 inline thread_local cudaStream_t g_alloc_stream = nullptr;
 inline thread_local bool g_alloc_async = false;
 
+// The library's own stream-ordered memory pool on the current device (engine.cu): created on first use with release
+// threshold = max, so freed blocks are handed out again by the next engine or batch, and the host application's
+// default pool (and its cudaMalloc) is left alone; wmh_trim_memory returns the cached blocks to the driver.
+cudaError_t pool_malloc_async(void** ptr, size_t bytes, cudaStream_t stream);
+
 // Owning device allocation.  Not copyable.
 template <class T>
 struct DeviceBuffer
@@ -85,7 +90,7 @@ struct DeviceBuffer
         if (n == 0) return;
         async = g_alloc_async;
         stream = g_alloc_stream;
-        cudaError_t e = async ? cudaMallocAsync((void**) &ptr, n * sizeof(T), stream) : cudaMalloc((void**) &ptr, n * sizeof(T));
+        cudaError_t e = async ? pool_malloc_async((void**) &ptr, n * sizeof(T), stream) : cudaMalloc((void**) &ptr, n * sizeof(T));
         if (e != cudaSuccess)
         {
             ptr = nullptr;

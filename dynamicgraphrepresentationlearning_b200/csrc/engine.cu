@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 
 using namespace wharf;
@@ -53,6 +54,48 @@ int wharf::report_failure(int code, const std::string& msg) { return fail(code, 
 
 namespace
 {
+constexpr int kMaxDevices = 64;
+cudaMemPool_t g_pools[kMaxDevices] = {};
+std::mutex g_pools_mutex;
+
+// The library's pool on `device` (created on first use; lives as long as the process).
+cudaError_t library_pool(int device, cudaMemPool_t* out)
+{
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_pools_mutex);
+    if (!g_pools[device])
+    {
+        cudaMemPoolProps props{};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        cudaMemPool_t pool = nullptr;
+        cudaError_t e = cudaMemPoolCreate(&pool, &props);
+        if (e != cudaSuccess) return e;
+        unsigned long long threshold = ~0ull;              // keep freed blocks: the next batch / engine takes them again
+        e = cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+        if (e != cudaSuccess) { cudaMemPoolDestroy(pool); return e; }
+        g_pools[device] = pool;
+    }
+    *out = g_pools[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+cudaError_t wharf::pool_malloc_async(void** ptr, size_t bytes, cudaStream_t stream)
+{
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return e;
+    cudaMemPool_t pool = nullptr;
+    e = library_pool(device, &pool);
+    if (e != cudaSuccess) return e;
+    return cudaMallocFromPoolAsync(ptr, bytes, pool, stream);
+}
+
+namespace
+{
 void peer_release(PeerLink& link)
 {
     for (u32 g = 0; g < kPeerMaxWorld; g++)
@@ -68,10 +111,24 @@ void peer_release(PeerLink& link)
 }
 }  // namespace
 
+// Declared first in wmh_engine, so destroyed last: every buffer of the engine frees itself on this stream.
+struct OwnedStream
+{
+    cudaStream_t handle = nullptr;
+    int device = 0;
+    ~OwnedStream()
+    {
+        if (!handle) return;
+        cudaSetDevice(device);
+        cudaStreamDestroy(handle);           // pending frees complete first: the driver releases the stream afterwards
+    }
+};
+
 struct wmh_engine
 {
+    OwnedStream owned;
     wmh_config cfg{};
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;        // = owned.handle
     cudaStream_t copy_stream = nullptr;   // corpus export overlapped with generation (generate_and_export)
     int sm_count = 148;
     u64 launches = 0, library_calls = 0;
@@ -102,6 +159,9 @@ struct wmh_engine
     u64 last_steps = 0;
     double timers[5] = {0, 0, 0, 0, 0};
     double last_walk_kernel_ms = 0;
+    double last_index_ms = 0;          // index build (generate) / index maintenance (batch) of the last call, device time
+    u32 last_search = 0;               // how the last batch found its affected walks: WMH_SEARCH_INDEX / WMH_SEARCH_SCAN, 0 = none
+    cudaEvent_t ev_index[2] = {nullptr, nullptr};
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     DeviceBuffer<u32> small;           // misc tiny results
     PeerLink peer;                     // exchange buffers of the box's ranks (wmh_peer_*)
@@ -124,7 +184,8 @@ struct wmh_engine
         g_alloc_stream = stream;
         coalesced_plan_release(coalesced_plan);
         for (auto& e : ev) if (e) cudaEventDestroy(e);
-        // buffers release in their destructors; the stream goes last
+        for (auto& e : ev_index) if (e) cudaEventDestroy(e);
+        // buffers release in their destructors (stream-ordered frees); `owned` goes last and destroys the stream
     }
 };
 
@@ -164,23 +225,23 @@ std::unique_ptr<wmh_engine> make_engine(const wmh_config* cfg)
     if (major < 10) throw CudaError(cudaErrorInvalidDevice, "device " + std::to_string(cfg->device) + " is not sm_100-class; this library carries sm_100a code only");
     eng->sm_count = sms;
     tr.mark("create: device properties");
-    // Random 32-byte sector gathers dominate this path: stop L2 from widening every miss into a larger DRAM fetch
-    // (measured on B200: 86 B of DRAM traffic per 32 B request at the default granularity; profiles/r01b_*).
+    // Process-wide device state is left alone.  Tuning aid only: WHARF_L2_FETCH=32|64|128 sets
+    // cudaLimitMaxL2FetchGranularity (measured on B200: the hint changes nothing for this path, profiles/r01c_*).
+    if (const char* env = std::getenv("WHARF_L2_FETCH"))
     {
-        size_t granularity = 32;
-        if (const char* env = std::getenv("WHARF_L2_FETCH")) granularity = (size_t) std::atoi(env);
-        if (granularity) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, granularity);
+        if (const size_t granularity = (size_t) std::atoi(env)) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, granularity);
         cudaGetLastError();
     }
-    tr.mark("create: L2 fetch limit");
-    WHARF_CUDA(cudaStreamCreateWithFlags(&eng->stream, cudaStreamNonBlocking));
+    WHARF_CUDA(cudaStreamCreateWithFlags(&eng->owned.handle, cudaStreamNonBlocking));
+    eng->owned.device = cfg->device;
+    eng->stream = eng->owned.handle;
     eng->bind();
     for (auto& ev : eng->ev) WHARF_CUDA(cudaEventCreate(&ev));
-    // keep stream-ordered scratch in the pool between batches
-    cudaMemPool_t pool;
-    WHARF_CUDA(cudaDeviceGetDefaultMemPool(&pool, cfg->device));
-    unsigned long long threshold = ~0ull;
-    WHARF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+    for (auto& ev : eng->ev_index) WHARF_CUDA(cudaEventCreate(&ev));
+    {
+        cudaMemPool_t pool = nullptr;                    // the library's own pool (pool_malloc_async), not the default one
+        WHARF_CUDA(library_pool(cfg->device, &pool));
+    }
     eng->d_steps.allocate(1);
     eng->small.allocate(16);
     tr.mark("create: stream+events+pool");
@@ -202,6 +263,19 @@ void finish_graph(wmh_engine& e, u64 n, u64 m, const u64* d_offsets, const u32* 
     e.g.pool.allocate(capacity);
     e.g.version.allocate(n);
     WHARF_CUDA(cudaMemsetAsync(e.g.version.ptr, 0, n * sizeof(u32), e.stream));
+    if (d_offsets)
+    {
+        // the constructor's contract (wharfmh.h:58-103): a bad id or an unsorted row would send every walk kernel out of
+        // bounds or silently break the sorted-set merges and searches - refuse it before anything can walk
+        WHARF_CUDA(cudaMemsetAsync(e.small.ptr, 0, 4, e.stream));
+        graph_check_csr(lc, d_offsets, n, m, d_edges, e.small.ptr);
+        u32 bad = 0;
+        WHARF_CUDA(cudaMemcpyAsync(&bad, e.small.ptr, 4, cudaMemcpyDeviceToHost, e.stream));
+        WHARF_CUDA(cudaStreamSynchronize(e.stream));
+        if (bad & 1u) throw std::invalid_argument("CSR offsets must start at 0, be non-decreasing and stay <= m");
+        if (bad & 2u) throw std::invalid_argument("CSR names a neighbour id >= number_of_vertices()");
+        if (bad & 4u) throw std::invalid_argument("CSR rows must be strictly ascending (sorted, no duplicates)");
+    }
     if (m) WHARF_CUDA(cudaMemcpyAsync(e.g.pool.ptr, d_edges, m * sizeof(u32), cudaMemcpyDeviceToDevice, e.stream));
     if (d_offsets) graph_build_desc(lc, d_offsets, n, m, e.g.desc.ptr);
     else WHARF_CUDA(cudaMemsetAsync(e.g.desc.ptr, 0, n * sizeof(RowDesc), e.stream));
@@ -340,6 +414,19 @@ void generate_and_export(wmh_engine& e, u32* host_out)
     for (cudaEvent_t ev : events) cudaEventDestroy(ev);
 }
 
+// index_build between two events on the engine stream: e.last_index_ms.
+void timed_index_build(wmh_engine& e)
+{
+    auto lc = e.lc();
+    WHARF_CUDA(cudaEventRecord(e.ev_index[0], e.stream));
+    index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+    WHARF_CUDA(cudaEventRecord(e.ev_index[1], e.stream));
+    WHARF_CUDA(cudaEventSynchronize(e.ev_index[1]));
+    float ms = 0;
+    WHARF_CUDA(cudaEventElapsedTime(&ms, e.ev_index[0], e.ev_index[1]));
+    e.last_index_ms = ms;
+}
+
 void generate(wmh_engine& e, u32* host_out = nullptr)
 {
     e.bind();
@@ -416,7 +503,8 @@ void generate(wmh_engine& e, u32* host_out = nullptr)
     e.last_steps = steps;
     e.have_walks = true;
     tr.mark("generate: walk (+export)");
-    if (e.cfg.search_mode == WMH_SEARCH_INDEX) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+    e.last_index_ms = 0;
+    if (e.cfg.search_mode == WMH_SEARCH_INDEX) timed_index_build(e);     // the reference builds it inside this call (wharfmh.h:312-354)
 }
 
 // Shared body of insert_edges_batch / delete_edges_batch (wharfmh.h:439-576 / 588-726).
@@ -427,6 +515,8 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
     e.n_touched = 0;
     e.last_steps = 0;
     e.last_walk_kernel_ms = 0;
+    e.last_index_ms = 0;
+    e.last_search = 0;
     if (count == 0) return;
 
     WHARF_CUDA(cudaMemsetAsync(e.small.ptr, 0, 4, e.stream));
@@ -460,7 +550,7 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
         bool use_index = false;
         if (e.cfg.search_mode == WMH_SEARCH_INDEX)
         {
-            if (!e.index.valid) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+            if (!e.index.valid) timed_index_build(e);
             use_index = true;
         }
         else if (e.cfg.search_mode == WMH_SEARCH_AUTO && e.index.valid)
@@ -468,6 +558,7 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
             const u64 visited = index_count_touched(lc, e.index, batch.sources.ptr, batch.n_sources);
             use_index = visited * 8 < e.w_local * e.walks_L;    // a random index entry costs about 8 streamed cells
         }
+        e.last_search = use_index ? WMH_SEARCH_INDEX : WMH_SEARCH_SCAN;
         if (use_index)
         {
             fill_u32(lc, e.min_pos.ptr, e.w_local, kNoPos);
@@ -495,7 +586,7 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
             WHARF_CUDA(cudaEventElapsedTime(&walk_kernel_ms, e.ev[3], e.ev[4]));
             // 3. index maintenance (wharfmh.h:861-922): the sorted index is re-derived from the patched corpus
             e.index.valid = false;
-            if (e.cfg.search_mode == WMH_SEARCH_INDEX) index_build(lc, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.index);
+            if (e.cfg.search_mode == WMH_SEARCH_INDEX) timed_index_build(e);
         }
     }
     WHARF_CUDA(cudaEventRecord(e.ev[2], e.stream));
@@ -677,13 +768,9 @@ int wmh_create_empty(wmh_engine** out, uint64_t n, const wmh_config* cfg)
 void wmh_destroy(wmh_engine* e)
 {
     if (!e) return;
-    cudaStream_t s = e->stream;
-    int device = e->cfg.device;
-    delete e;
+    delete e;                             // the engine owns its stream (OwnedStream)
     g_alloc_stream = nullptr;
     g_alloc_async = false;
-    cudaSetDevice(device);
-    if (s) cudaStreamDestroy(s);
 }
 
 int wmh_destroy_index(wmh_engine* e)
@@ -828,11 +915,28 @@ int wmh_affected_walks(wmh_engine* e, uint64_t* ids, uint32_t* positions, uint64
         e->bind();
         const u64 k = e->n_affected;
         if (k == 0) return (int) WMH_OK;
-        std::vector<u32> local(k);
-        WHARF_CUDA(cudaMemcpyAsync(local.data(), e->aff_ids.ptr, k * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
+        Scratch<u64> d_global;
+        if (ids)
+        {
+            d_global.allocate(e->stream, k);
+            walks_global_ids(e->lc(), e->map, e->aff_ids.ptr, k, d_global.ptr);
+            WHARF_CUDA(cudaMemcpyAsync(ids, d_global.ptr, k * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+        }
         if (positions) WHARF_CUDA(cudaMemcpyAsync(positions, e->aff_pos.ptr, k * sizeof(u32), cudaMemcpyDeviceToHost, e->stream));
         WHARF_CUDA(cudaStreamSynchronize(e->stream));
-        if (ids) for (u64 i = 0; i < k; i++) ids[i] = local_to_global(*e, local[i]);
+        return (int) WMH_OK;
+    });
+}
+
+int wmh_affected_walks_global_device(wmh_engine* e, uint64_t* d_ids, uint64_t capacity)
+{
+    if (!e) return fail(WMH_ERR_INVALID, "null engine");
+    if (capacity < e->n_affected) return fail(WMH_ERR_RANGE, "affected-walk buffer too small");
+    if (e->n_affected && !d_ids) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        e->bind();
+        walks_global_ids(e->lc(), e->map, e->aff_ids.ptr, e->n_affected, d_ids);
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
         return (int) WMH_OK;
     });
 }
@@ -1110,10 +1214,10 @@ int wmh_compressed_walks(wmh_engine* e, uint64_t* ptr, uint64_t* codes, uint64_t
         try { ensure_codes(*e); }
         catch (const std::domain_error& d) { return fail(WMH_ERR_DOMAIN, d.what()); }
         if (total) *total = e->index.entries;
+        if (codes && capacity < e->index.entries) return fail(WMH_ERR_RANGE, "code buffer too small");   // before any output is written
         if (ptr) WHARF_CUDA(cudaMemcpyAsync(ptr, e->index.ptr.ptr, (e->g.n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
         if (codes)
         {
-            if (capacity < e->index.entries) return fail(WMH_ERR_RANGE, "code buffer too small");
             if (e->index.entries) WHARF_CUDA(cudaMemcpyAsync(codes, e->codes.ptr, e->index.entries * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
         }
         WHARF_CUDA(cudaStreamSynchronize(e->stream));
@@ -1200,6 +1304,8 @@ int wmh_memory_footprint(wmh_engine* e, wmh_memory* out)
 
 uint64_t wmh_kernel_launches(const wmh_engine* e) { return e ? e->launches : 0; }
 double wmh_last_walk_kernel_ms(const wmh_engine* e) { return e ? e->last_walk_kernel_ms : 0.0; }
+double wmh_last_index_ms(const wmh_engine* e) { return e ? e->last_index_ms : 0.0; }
+uint32_t wmh_last_search_mode(const wmh_engine* e) { return e ? e->last_search : 0u; }
 const uint32_t* wmh_device_walks(const wmh_engine* e) { return (e && e->have_walks) ? e->walks.ptr : nullptr; }
 void* wmh_stream(const wmh_engine* e) { return e ? (void*) e->stream : nullptr; }
 
@@ -1281,8 +1387,8 @@ int wmh_trim_memory(int device)
     return guarded([&] {
         DefaultCtx ctx(device);
         WHARF_CUDA(cudaDeviceSynchronize());
-        cudaMemPool_t pool;
-        WHARF_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        cudaMemPool_t pool = nullptr;
+        WHARF_CUDA(library_pool(device, &pool));
         WHARF_CUDA(cudaMemPoolTrimTo(pool, 0));
         return (int) WMH_OK;
     });

@@ -71,7 +71,7 @@ struct Scratch
         release();
         stream = s;
         count = n;
-        cudaError_t e = cudaMallocAsync((void**) &ptr, (n ? n : 1) * sizeof(T), s);
+        cudaError_t e = pool_malloc_async((void**) &ptr, (n ? n : 1) * sizeof(T), s);
         if (e != cudaSuccess)
         {
             ptr = nullptr;
@@ -150,6 +150,8 @@ void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g);
 void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g);
 void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g);
 void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr /* n+1 */, u32* d_col /* m */);
+// flag |= 1: offsets not monotone / beyond m; 2: a neighbour id >= n; 4: a row not strictly ascending.
+void graph_check_csr(const LaunchCtx& lc, const u64* d_offsets_n, u64 n, u64 m, const u32* d_edges, u32* d_flag);
 void graph_check_ids(const LaunchCtx& lc, const u32* d_pairs, u64 count, u64 n, u32* d_flag);
 void rmat_generate_device(const LaunchCtx& lc, u64 edges_number, u64 vertices_number, u64 batch_seed, bool self_loops,
                           bool directed, double a, double b, double c, u32* d_out, u64* count_out);
@@ -197,6 +199,8 @@ u64  walks_compact_affected(const LaunchCtx& lc, const u32* d_min_pos, u64 w_loc
 void walks_transpose_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 first, u64 count, u32* d_out);
 void walks_gather_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_ids, u64 count, u32* d_out);
 void walks_fingerprint(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, unsigned long long* d_sum);
+// out[i] = global walk id of local walk local_ids[i] (ascending local ids give ascending global ids).
+void walks_global_ids(const LaunchCtx& lc, const ShardMap& map, const u32* d_local_ids, u64 count, u64* d_out);
 void fill_u32(const LaunchCtx& lc, u32* d, u64 count, u32 value);
 
 // ---- index kernels (kernels_index.cu) -------------------------------------------------------------

@@ -36,6 +36,32 @@ __global__ void build_desc_kernel(const u64* __restrict__ offsets, u64 n, u64 m,
     desc[v] = RowDesc{(u32) lo, (u32) (hi - lo)};
 }
 
+// The constructor's contract (graph/wharfmh.h:58-103: rows sorted and unique, ids < n): offsets monotone and <= m,
+// every neighbour < n, every row strictly ascending.  One thread per edge slot finds its row by binary search over the
+// n offsets; flag bit 0 = offsets, bit 1 = neighbour id, bit 2 = row order.
+__global__ void __launch_bounds__(256) check_csr_kernel(const u64* __restrict__ offsets, u64 n, u64 m, const u32* __restrict__ edges, u32* __restrict__ flag)
+{
+    const u64 t = (u64) blockIdx.x * 256 + threadIdx.x;
+    if (t < n)
+    {
+        const u64 lo = offsets[t];
+        const u64 hi = (t + 1 == n) ? m : offsets[t + 1];
+        if (lo > hi || hi > m || (t == 0 && lo != 0)) atomicOr(flag, 1u);
+    }
+    if (t >= m) return;
+    const u32 x = edges[t];
+    if (x >= n) atomicOr(flag, 2u);
+    if (t == 0) return;
+    // same row as the previous slot <=> no offset equals t: largest v with offsets[v] <= t
+    u64 lo = 0, hi = n;
+    while (hi - lo > 1)
+    {
+        const u64 mid = (lo + hi) >> 1;
+        if (offsets[mid] <= t) lo = mid; else hi = mid;
+    }
+    if (offsets[lo] < t && edges[t - 1] >= x) atomicOr(flag, 4u);
+}
+
 __global__ void check_ids_kernel(const u32* __restrict__ pairs, u64 count2, u64 n, u32* __restrict__ flag)
 {
     for (u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x; i < count2; i += (u64) gridDim.x * blockDim.x)
@@ -428,6 +454,15 @@ void graph_build_desc(const LaunchCtx& lc, const u64* d_offsets_n, u64 n, u64 m,
 {
     if (n == 0) return;
     build_desc_kernel<<<div_up(n, 256), 256, 0, lc.stream>>>(d_offsets_n, n, m, d_desc);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void graph_check_csr(const LaunchCtx& lc, const u64* d_offsets_n, u64 n, u64 m, const u32* d_edges, u32* d_flag)
+{
+    const u64 work = n > m ? n : m;
+    if (work == 0) return;
+    check_csr_kernel<<<div_up(work, 256), 256, 0, lc.stream>>>(d_offsets_n, n, m, d_edges, d_flag);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
 }

@@ -636,16 +636,26 @@ __global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParam
 }
 
 // Eight lanes per row: tails of the rows other ranks computed <- the words they stored into the own exchange buffer.
+// A barrier that gave up waiting (error word set) means the window may hold words of an earlier pass or only part of
+// this one: the caches are then left EMPTY (0 = lazy first-touch init in the walk kernel) instead of imported.  Every
+// word is zeroed once read, so a later pass can never import a stale valid entry either.
 __global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
-                                                               const u32* __restrict__ split, const unsigned short* __restrict__ received, u32 n, u32 rank)
+                                                               const u32* __restrict__ split, unsigned short* __restrict__ received, u32 n, u32 rank,
+                                                               const u32* __restrict__ error_word)
 {
     const u64 t = (u64) blockIdx.x * 256 + threadIdx.x;
     const u32 v = (u32) (t >> 3), sub = threadIdx.x & 7;
     if (v >= n || (v >= split[rank] && v < split[rank + 1])) return;
+    const bool failed = *reinterpret_cast<const volatile u32*>(error_word) != 0;
     const RowDesc d = load_desc(desc, v);
-    const unsigned short* src = received + __ldg(eoff + v);
+    unsigned short* src = received + __ldg(eoff + v);
     unsigned short* halves = reinterpret_cast<unsigned short*>(pool + d.begin);                // low half of aux word i = halves[4 i + 2]
-    for (u32 i = sub; i < d.degree; i += 8) halves[4 * (u64) i + 2] = __ldcs(src + i);
+    for (u32 i = sub; i < d.degree; i += 8)
+    {
+        const unsigned short word = src[i];
+        src[i] = 0;
+        halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : word;
+    }
 }
 
 // Flag barrier in peer memory: lane g tells rank g "rank `rank` reached epoch", then waits for rank g's word in the
@@ -772,6 +782,13 @@ __global__ void __launch_bounds__(256) fingerprint_kernel(const u32* __restrict_
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
     if ((threadIdx.x & 31) == 0 && h) atomicAdd(sum, (unsigned long long) h);
+}
+
+// Global walk id (replica * n + start vertex) of local walks: the ids insert/delete_edges_batch return (wharfmh.h:548,698).
+__global__ void global_ids_kernel(ShardMap map, const u32* __restrict__ local_ids, u64 count, u64* __restrict__ out)
+{
+    const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = map.global_id(local_ids[i]);
 }
 
 __global__ void fill_u32_kernel(u32* __restrict__ d, u64 count, u32 value)
@@ -920,6 +937,14 @@ void walks_fingerprint(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32
     WHARF_CUDA(cudaGetLastError());
 }
 
+void walks_global_ids(const LaunchCtx& lc, const ShardMap& map, const u32* d_local_ids, u64 count, u64* d_out)
+{
+    if (count == 0) return;
+    global_ids_kernel<<<div_up(count, 256), 256, 0, lc.stream>>>(map, d_local_ids, count, d_out);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
 void fill_u32(const LaunchCtx& lc, u32* d, u64 count, u32 value)
 {
     if (count == 0) return;
@@ -957,7 +982,8 @@ void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, Pe
     lc.count(2);
     peer_barrier(lc, link);                                    // every rank's words have arrived
     n2v_share_import_kernel<<<div_up((u64) n * 8, 256), 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, split.ptr,
-                                                                             reinterpret_cast<const unsigned short*>(link.own() + kPeerFlagBytes), n, link.rank);
+                                                                             reinterpret_cast<unsigned short*>(link.own() + kPeerFlagBytes), n, link.rank,
+                                                                             reinterpret_cast<const u32*>(link.own() + kPeerErrorOffset));
     lc.count();
     peer_barrier(lc, link);                                    // nobody overwrites a buffer that is still being read
     WHARF_CUDA(cudaGetLastError());

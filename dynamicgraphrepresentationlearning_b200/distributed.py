@@ -61,6 +61,24 @@ class ShardedWharfMH:
                 connect_peers(self.engine, group)
         else:
             self.engine = engine_factory(cfg)
+        self.last_timing: dict = {}
+
+    @classmethod
+    def from_engine(cls, engine: WharfMH, group=None) -> "ShardedWharfMH":
+        """Wraps the engine this rank already built (its config carries rank/world): the exchanges run on the same object
+        that generated the corpus."""
+        self = cls.__new__(cls)
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        if engine.config.rank != self.rank or engine.config.world != self.world:
+            raise ValueError("the engine was created for another rank / world")
+        self.config = engine.config
+        self._on_gpu = dist.get_backend(group) == "nccl"
+        self.device = torch.device(f"cuda:{engine.config.device}") if self._on_gpu else torch.device("cpu")
+        self.engine = engine
+        self.last_timing = {}
+        return self
 
     # -- helpers --------------------------------------------------------------------------------------
     def _all_reduce_sum(self, value: int) -> int:
@@ -110,26 +128,59 @@ class ShardedWharfMH:
         """graph/wharfmh.h:250 on every shard; returns the global number of walker steps."""
         return self._all_reduce_sum(self.engine.generate_initial_random_walks())
 
-    def _update(self, edges, delete: bool, remove_dups: bool, apply_walk_updates: bool, src: int) -> np.ndarray:
-        batch = self.broadcast_batch(edges, src)
-        m = int(batch.shape[0])
-        if self._on_gpu:
-            fn = self.engine.delete_edges_batch_device if delete else self.engine.insert_edges_batch_device
-            torch.cuda.current_stream().synchronize()          # the engine runs on its own stream
-            fn(batch.data_ptr(), m, remove_dups=remove_dups, apply_walk_updates=apply_walk_updates)
-            local = self.engine.affected_walks()[0]
-        else:
+    def all_gather_ids_device(self, local: torch.Tensor) -> torch.Tensor:
+        """C2 without leaving the device: `local` = this rank's affected global ids (int64 device tensor); returns the
+        ascending ids of all ranks as a device tensor (counts, one padded NCCL all-gather, device sort)."""
+        counts = torch.zeros(self.world, dtype=torch.int64, device=self.device)
+        mine = torch.tensor([local.shape[0]], dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(counts, mine, group=self.group)
+        host_counts = counts.tolist()
+        width = max(host_counts)
+        if width == 0:
+            return torch.empty(0, dtype=torch.int64, device=self.device)
+        padded = torch.empty(width, dtype=torch.int64, device=self.device)
+        padded[: local.shape[0]] = local
+        gathered = torch.empty(self.world * width, dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(gathered, padded, group=self.group)
+        parts = [gathered[r * width: r * width + host_counts[r]] for r in range(self.world)]
+        return torch.sort(torch.cat(parts)).values
+
+    def _update(self, edges, delete: bool, remove_dups: bool, apply_walk_updates: bool, src: int, return_device: bool = False):
+        import time
+        if not self._on_gpu:
+            batch = self.broadcast_batch(edges, src)
             fn = self.engine.delete_edges_batch if delete else self.engine.insert_edges_batch
             local = fn(batch.numpy().view(np.uint32).copy(), sorted=False, remove_dups=remove_dups, apply_walk_updates=apply_walk_updates)
-        return self.all_gather_ids(np.asarray(local, dtype=np.uint64))
+            return self.all_gather_ids(np.asarray(local, dtype=np.uint64))
+        t0 = time.perf_counter()
+        batch = self.broadcast_batch(edges, src)                  # C1
+        torch.cuda.current_stream().synchronize()                  # the engine runs on its own stream
+        t1 = time.perf_counter()
+        fn = self.engine.delete_edges_batch_device if delete else self.engine.insert_edges_batch_device
+        k = fn(batch.data_ptr(), int(batch.shape[0]), remove_dups=remove_dups, apply_walk_updates=apply_walk_updates)
+        t2 = time.perf_counter()
+        local = torch.empty(max(k, 1), dtype=torch.int64, device=self.device)
+        self.engine.affected_walks_global_device(local.data_ptr(), local.shape[0])
+        ids = self.all_gather_ids_device(local[:k])                # C2
+        torch.cuda.current_stream().synchronize()
+        t3 = time.perf_counter()
+        self.last_timing = {"bcast_ms": 1e3 * (t1 - t0), "update_ms": 1e3 * (t2 - t1), "allgather_ms": 1e3 * (t3 - t2),
+                            "local_affected": int(k), "global_affected": int(ids.shape[0])}
+        if return_device:
+            return ids
+        return ids.cpu().numpy().astype(np.uint64)
 
-    def insert_edges_batch(self, edges=None, remove_dups: bool = False, apply_walk_updates: bool = True, src: int = 0) -> np.ndarray:
-        """graph/wharfmh.h:439: `edges` is read on rank `src` only; returns the global affected walk ids (ascending)."""
-        return self._update(edges, False, remove_dups, apply_walk_updates, src)
+    def insert_edges_batch(self, edges=None, remove_dups: bool = False, apply_walk_updates: bool = True, src: int = 0,
+                           return_device: bool = False):
+        """graph/wharfmh.h:439: `edges` is read on rank `src` only; returns the global affected walk ids (ascending) on
+        every rank - a numpy array, or the device tensor the all-gather produced when return_device.  Under NCCL
+        `last_timing` holds the milliseconds of the broadcast, the local update and the all-gather."""
+        return self._update(edges, False, remove_dups, apply_walk_updates, src, return_device)
 
-    def delete_edges_batch(self, edges=None, remove_dups: bool = False, apply_walk_updates: bool = True, src: int = 0) -> np.ndarray:
+    def delete_edges_batch(self, edges=None, remove_dups: bool = False, apply_walk_updates: bool = True, src: int = 0,
+                           return_device: bool = False):
         """graph/wharfmh.h:588."""
-        return self._update(edges, True, remove_dups, apply_walk_updates, src)
+        return self._update(edges, True, remove_dups, apply_walk_updates, src, return_device)
 
     def walk(self, walk_id: int) -> str:
         """graph/wharfmh.h:365 for any global walk id: the owner broadcasts the text."""

@@ -191,6 +191,12 @@ class WharfMH:
         check(self._lib.wmh_affected_walks(self._h, _ptr(ids), _ptr(pos), k))
         return ids, pos
 
+    def affected_walks_global_device(self, d_out: int, capacity: int) -> int:
+        """Global ids (ascending) of the last batch's affected walks into device memory at `d_out` (u64 x capacity)."""
+        k = self.number_of_affected_walks()
+        check(self._lib.wmh_affected_walks_global_device(self._h, C.c_void_p(int(d_out)), int(capacity)))
+        return k
+
     def touched_vertices(self) -> np.ndarray:
         k = C.c_uint64()
         check(self._lib.wmh_touched_vertices(self._h, None, 0, C.byref(k)))
@@ -315,6 +321,13 @@ class WharfMH:
 
     def last_walk_kernel_ms(self) -> float:
         return float(self._lib.wmh_last_walk_kernel_ms(self._h))
+
+    def last_index_ms(self) -> float:
+        return float(self._lib.wmh_last_index_ms(self._h))
+
+    def last_search_mode(self) -> int:
+        """SEARCH_INDEX / SEARCH_SCAN as taken by the last batch (0: none)."""
+        return int(self._lib.wmh_last_search_mode(self._h))
 
     def device_walks_ptr(self) -> int:
         return int(self._lib.wmh_device_walks(self._h) or 0)

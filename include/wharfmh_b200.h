@@ -180,6 +180,9 @@ WMH_API int wmh_affected_walks(wmh_engine* e, uint64_t* ids, uint32_t* positions
 /* Device views of the same (local walk index -> use wmh_local_to_global_walk): valid until the next batch. */
 WMH_API int wmh_affected_walks_device(wmh_engine* e, const uint32_t** d_local_ids, const uint32_t** d_positions,
                                       uint64_t* count);
+/* The same ids (global, ascending) written to DEVICE memory (capacity >= the affected count): what a multi-rank caller
+ * hands to its all-gather without a trip through the host.  Complete when the call returns. */
+WMH_API int wmh_affected_walks_global_device(wmh_engine* e, uint64_t* d_ids, uint64_t capacity);
 /* Distinct source vertices of the last batch (the vertices whose walks were affected), ascending. */
 WMH_API int wmh_touched_vertices(wmh_engine* e, uint32_t* out, uint64_t capacity, uint64_t* count);
 
@@ -261,12 +264,18 @@ WMH_API int    wmh_memory_footprint(wmh_engine* e, wmh_memory* out);     /* grap
 WMH_API uint64_t wmh_kernel_launches(const wmh_engine* e);
 /* Device time (ms) of the dominant kernel of the last generate / update (walk kernel), and its launches. */
 WMH_API double   wmh_last_walk_kernel_ms(const wmh_engine* e);
+/* Device milliseconds the last call spent on the inverted index (walks/inverted_index.h): its build inside
+ * wmh_generate_initial_random_walks (graph/wharfmh.h:312-354) or its maintenance inside a batch (wharfmh.h:861-922);
+ * 0 when the call did not touch the index (search_mode SCAN, or AUTO without an index). */
+WMH_API double   wmh_last_index_ms(const wmh_engine* e);
+/* How the last batch found its affected walks: WMH_SEARCH_INDEX or WMH_SEARCH_SCAN as TAKEN (0: no search ran). */
+WMH_API uint32_t wmh_last_search_mode(const wmh_engine* e);
 /* Raw device pointers for zero-copy consumers (position-major walk matrix [L][local_walks]). */
 WMH_API const uint32_t* wmh_device_walks(const wmh_engine* e);
 WMH_API void*    wmh_stream(const wmh_engine* e);                        /* cudaStream_t */
 WMH_API int      wmh_synchronize(wmh_engine* e);
-/* Engines allocate stream-ordered from the device's default memory pool and leave freed blocks there for the next
- * engine / batch (the analogue of the reference's static allocator pools, graph/wharfmh.h:1041-1047, which are
+/* Engines allocate stream-ordered from the library's own memory pool on the device (the host application's default
+ * pool is left alone) and leave freed blocks there for the next engine / batch (the analogue of the reference's static allocator pools, graph/wharfmh.h:1041-1047, which are
  * never returned either).  This hands every unused block back to the driver. */
 WMH_API int      wmh_trim_memory(int device);
 

@@ -671,6 +671,30 @@ WO_API const u32* wo_affected_pos(const wo_engine* e)  { return e->affected_pos;
 WO_API u64        wo_steps_last(const wo_engine* e)    { return e->steps_last; }
 WO_API u32        wo_sampler_init_value(const wo_engine* e, u32 cur, u32 aux) { return sampler_init_value(e, cur, aux); }
 
+/* Checksum of checksums: the wrapping sum over walks of the FNV-1a-64 of each walk's own text form "v0 v1 ... "
+ * (graph/wharfmh.h:365-394, no line break).  A sum does not depend on the order of the walks, so the fingerprints of
+ * the shards of a partitioned corpus add up to the fingerprint of the whole (tests compare wmh_corpus_fingerprint). */
+WO_API u64 wo_corpus_fingerprint(const u32* walks, u64 n_walks, u32 L)
+{
+    u64 sum = 0;
+    char buf[16];
+    for (u64 w = 0; w < n_walks; w++)
+    {
+        u64 h = UINT64_C(0xcbf29ce484222325);
+        for (u32 p = 0; p < L; p++)
+        {
+            u32 v = walks[w * L + p];
+            if (v == WO_NO_VERTEX) break;
+            int len = 0;
+            do { buf[len++] = (char) ('0' + v % 10); v /= 10; } while (v);
+            while (len) { h ^= (unsigned char) buf[--len]; h *= UINT64_C(0x100000001b3); }
+            h ^= (unsigned char) ' '; h *= UINT64_C(0x100000001b3);
+        }
+        sum += h;
+    }
+    return sum;
+}
+
 /* FNV-1a-64 over the text form the reference's walk() emits ("v0 v1 ... " + '\n', wharfmh.h:365-394):
  * the corpus fingerprint used by the golden vectors of SURVEY.md 8c. */
 WO_API u64 wo_corpus_fnv1a(const u32* walks, u64 n_walks, u32 L)

@@ -92,6 +92,8 @@ def lib() -> C.CDLL:
         L.wo_sampler_init_value.restype = u32
         L.wo_corpus_fnv1a.argtypes = [p, u64, u32]
         L.wo_corpus_fnv1a.restype = u64
+        L.wo_corpus_fingerprint.argtypes = [p, u64, u32]
+        L.wo_corpus_fingerprint.restype = u64
         L.wo_threads.restype = C.c_int
         _lib = L
     return _lib
@@ -147,6 +149,12 @@ def csr_from_sorted_pairs(n: int, pairs: np.ndarray) -> tuple[np.ndarray, np.nda
 def corpus_hash(walks: np.ndarray) -> int:
     walks = np.ascontiguousarray(walks, dtype=np.uint32)
     return int(lib().wo_corpus_fnv1a(_ptr(walks), walks.shape[0], walks.shape[1]))
+
+
+def corpus_fingerprint(walks: np.ndarray) -> int:
+    """Wrapping sum of the per-walk FNV-1a of the text form: what wmh_corpus_fingerprint computes on the device."""
+    walks = np.ascontiguousarray(walks, dtype=np.uint32)
+    return int(lib().wo_corpus_fingerprint(_ptr(walks), walks.shape[0], walks.shape[1]))
 
 
 class Oracle:

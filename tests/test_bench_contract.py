@@ -11,10 +11,26 @@ ROOT = Path(__file__).resolve().parents[1]
 sys.path.insert(0, str(ROOT))
 
 
+def bench_workloads():
+    import bench
+    return bench.WORKLOADS
+
+
+def test_default_run_puts_the_north_star_configuration_on_top():
+    """`python bench.py --gpus N --steps K --warmup W` (what the driver runs) must headline RMAT scale-25 DeepWalk and carry
+    the scale-20 node2vec MH block and the scale-14 pair of the reference arm."""
+    import bench
+    src = (ROOT / "bench.py").read_text()
+    assert 'ap.add_argument("--workload", default="all"' in src
+    assert 'run_workload(ctx, "dw25"' in src and '"n2v20": run_workload(ctx, "n2v20"' in src and '"dw14": run_workload(ctx, "dw14"' in src
+    assert bench.WORKLOADS["dw25"]["n"] == 1 << 25 and bench.WORKLOADS["dw25"]["det"] and bench.WORKLOADS["dw25"]["model"] == "deepwalk"
+    assert bench.REFERENCE_WORKLOAD == "dw14" and bench.WORKLOADS["dw14"]["edges_half"] == 8 * bench.WORKLOADS["dw14"]["n"]
+
+
 def test_reference_arm_prints_one_contract_line(wo):
     if not wo.ref_available():
         pytest.skip("oracle/_ref (the unmodified reference) is not built on this machine")
-    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-sample-scale", "12"],
+    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
                        capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
@@ -23,9 +39,11 @@ def test_reference_arm_prints_one_contract_line(wo):
     assert d["impl"] == "reference" and d["metric"] == "walk-steps/sec (init walks)" and d["unit"] == "walk-steps/s"
     assert d["higher_is_better"] is True and d["n_gpus"] == 1 and d["steps"] == 1 and d["warmup"] >= 3          # timing rules: W >= 3
     assert d["value"] > 0 and d["ms_per_step"] > 0 and d["vs_baseline"] is None and d["data"] == "synthetic"
-    assert "workload" in d["config"] and "node2vec MH" in d["config"]["workload"]
+    # the CPU arm runs BASELINE configs[0] in full: the size both arms share (the b200 line carries it as blocks.dw14)
+    assert d["config"]["workload"] == bench_workloads()["dw14"]["desc"] and d["config"]["deterministic_mode"] is True
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"] and "scale-12" in cb["sample"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"]
+    assert "the whole workload" in cb["sample"] and "scale-14" in cb["sample"] and "inverted index" in cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 

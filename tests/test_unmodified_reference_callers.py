@@ -167,3 +167,32 @@ def test_reference_memory_footprint_driver_on_gpu(cora, tmp_path):
     r = subprocess.run([str(exe), "-f", str(tmp_path / "cora.adj"), "-model", "node2vec", "-det", "false"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "Walking model: NODE2VEC" in r.stdout and "Vertices: 2708, Edges: 10556" in r.stdout and "Device memory" in r.stdout
+
+
+@pytest.mark.gpu
+def test_reference_own_wharfmh_tests_on_gpu(tmp_path):
+    """The reference's own tests/wharfmh.cpp (/root/reference/tests/wharfmh.cpp:56-186 and on: constructors, degrees, destroy,
+    edge counts, walk generation, insert/delete batches), compiled UNCHANGED against include/compat + the library, run on the
+    device.  Its fixture shells out to ./SNAPtoAdj on data/flickr-graph, a file the reference does not ship: here
+    ./SNAPtoAdj is this package's replacement (graph_io, symmetrise/dedup on the device) and the data file is cora's edge
+    list from the reference's own experiments/data."""
+    import os
+    import sys
+    import numpy as np
+    exe = brc.OUT / "ref_test_wharfmh"
+    if not exe.exists():
+        pytest.skip("reference callers were not built where the snapshot was taken")
+    (tmp_path / "data").mkdir()
+    pairs = np.load(ROOT / "tests" / "golden" / "cora_edge_list.npz")["pairs"]
+    (tmp_path / "data" / "flickr-graph").write_text("".join(f"{u} {v}\n" for u, v in pairs.tolist()))
+    snap = tmp_path / "SNAPtoAdj"
+    snap.write_text(f'#!/bin/sh\nPYTHONPATH={ROOT} exec {sys.executable} -m dynamicgraphrepresentationlearning_b200.graph_io "$@"\n')
+    snap.chmod(0o755)
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=1500, cwd=tmp_path, env=dict(os.environ, MINI_GTEST_FILTER=""))
+    lines = [l for l in r.stdout.splitlines() if l.startswith("[")]
+    total = [l for l in lines if l.startswith("[  TOTAL   ]")]
+    assert total, (r.stdout[-3000:], r.stderr[-3000:])
+    ran, failures = (int(x) for x in re.findall(r"(\d+) tests, (\d+) failures", total[-1])[0])
+    failed = [l for l in lines if l.startswith("[  FAILED  ]")]
+    assert r.returncode == 0 and failures == 0 and not failed, (failed, r.stdout[-3000:], r.stderr[-3000:])
+    assert ran >= 10

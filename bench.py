@@ -438,7 +438,7 @@ def run_e2e(ctx, spec, cfg, n, m, d_offsets, d_edges, iters):
     out = {"value": ctx.sum_over_ranks(e_steps) / e2e_s, "unit": "walk-steps/s",
            "h2d_bytes_per_step": int(n * 8 + m * 4), "d2h_bytes_per_step": int(corpus_bytes),
            "iters": iters, "ms_per_step": 1e3 * e2e_s / iters, "pin_host_buffers_s": round(pin_s, 2),
-           "phases_ms_last": dict(zip(("create_h2d", "generate_to_host", "destroy"), phases[-1])),
+           "phases_ms": {"order": ["create_h2d", "generate_to_host", "destroy"], "warm": phases[0], "timed": phases[1:]},
            "path": "wmh_create(host CSR) + wmh_generate_initial_random_walks_to_host(pinned host: whole corpus D2H overlapped with the walk kernels) + wmh_destroy, per rank"}
     for a in (h_walks_np, h_off_np, h_adj_np):
         pinned_release(torch, a)
@@ -760,7 +760,7 @@ def main():
             "parity_check": parity,
         }
         for k in ("per_walker_kernel", "deterministic_mode"):
-            if k in head:
+            if isinstance(head.get(k), dict):
                 line[k] = head[k]
         if blocks:
             line["blocks"] = blocks

@@ -84,6 +84,7 @@ SIGNATURES = {
     "wmh_affected_walks": (i32, [vp, vp, vp, u64]),
     "wmh_affected_walks_device": (i32, [vp, C.POINTER(vp), C.POINTER(vp), PU64]),
     "wmh_affected_walks_global_device": (i32, [vp, vp, u64]),
+    "wmh_sampler_chain": (i32, [vp, u32, u32, u64, PU32, vp, u64]),
     "wmh_touched_vertices": (i32, [vp, vp, u64, PU64]),
     "wmh_walk": (i32, [vp, u64, vp, PU32]),
     "wmh_walk_string": (i32, [vp, u64, vp, C.c_size_t, C.POINTER(C.c_size_t)]),

@@ -1131,6 +1131,31 @@ int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum)
     });
 }
 
+int wmh_sampler_chain(wmh_engine* e, uint32_t cur, uint32_t prev, uint64_t iters, uint32_t* init_value, uint64_t* counts, uint64_t capacity)
+{
+    if (!e || !counts) return fail(WMH_ERR_INVALID, "null argument");
+    if (cur >= e->g.n || prev >= e->g.n) return fail(WMH_ERR_RANGE, "vertex out of range");
+    return guarded([&] {
+        e->bind();
+        validate_config(e->cfg);
+        RowDesc d;
+        WHARF_CUDA(cudaMemcpyAsync(&d, e->g.desc.ptr + cur, sizeof(d), cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        if (capacity < d.degree) return fail(WMH_ERR_RANGE, "counts must hold degree(cur) entries");
+        Scratch<unsigned long long> d_counts(e->stream, std::max<u64>(1, d.degree));
+        Scratch<u32> d_init(e->stream, 1);
+        WHARF_CUDA(cudaMemsetAsync(d_counts.ptr, 0, std::max<u64>(1, d.degree) * 8, e->stream));
+        WalkParams wp = walk_params(*e);
+        sampler_chain(e->lc(), wp, cur, prev, iters, d_init.ptr, d_counts.ptr);
+        u32 init = kNoVertex;
+        WHARF_CUDA(cudaMemcpyAsync(&init, d_init.ptr, 4, cudaMemcpyDeviceToHost, e->stream));
+        if (d.degree) WHARF_CUDA(cudaMemcpyAsync(counts, d_counts.ptr, d.degree * 8, cudaMemcpyDeviceToHost, e->stream));
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        if (init_value) *init_value = init;
+        return (int) WMH_OK;
+    });
+}
+
 int wmh_build_index(wmh_engine* e)
 {
     if (!e) return fail(WMH_ERR_INVALID, "null engine");

@@ -199,6 +199,9 @@ u64  walks_compact_affected(const LaunchCtx& lc, const u32* d_min_pos, u64 w_loc
 void walks_transpose_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 first, u64 count, u32* d_out);
 void walks_gather_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_ids, u64 count, u32* d_out);
 void walks_fingerprint(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, unsigned long long* d_sum);
+// MetropolisHastingsSampler::sample as a chain on the fixed state (cur, prev): d_counts[j] (degree(cur) entries, zeroed by the
+// caller) += samples returning neighbour j; *d_init = the init value.
+void sampler_chain(const LaunchCtx& lc, const WalkParams& wp, u32 cur, u32 prev, u64 iters, u32* d_init, unsigned long long* d_counts);
 // out[i] = global walk id of local walk local_ids[i] (ascending local ids give ascending global ids).
 void walks_global_ids(const LaunchCtx& lc, const ShardMap& map, const u32* d_local_ids, u64 count, u64* d_out);
 void fill_u32(const LaunchCtx& lc, u32* d, u64 count, u32 value);

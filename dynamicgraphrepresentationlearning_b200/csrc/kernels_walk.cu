@@ -487,6 +487,60 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
     block_add_u64(steps_out, steps);
 }
 
+// MetropolisHastingsSampler::sample as a CHAIN (metropolis_hastings_sampler.h:31-46; fixture tests/sampler.cpp:86-127): one
+// sampler object of the fixed state (cur, prev) sampled `iters` times, its stored vertex advancing with every accepted
+// proposal (the walk kernels sample from copies, whose stored vertex never moves: see "Sampler cache" above).  One thread:
+// the chain is sequential by definition.  Membership by plain binary search, so it runs on either row layout.
+// counts[j] = samples that returned neighbour j of cur; *init_out = the init value (all three strategies, :69-108).
+__global__ void sampler_chain_kernel(DevWalkParams p, u32 model, u32 cur, u32 prev, u64 iters, u32* __restrict__ init_out,
+                                     unsigned long long* __restrict__ counts)
+{
+    if (blockIdx.x || threadIdx.x) return;
+    const RowDesc d = load_desc(p.desc, cur), dprev = load_desc(p.desc, prev);
+    if (d.degree == 0) { *init_out = kNoVertex; return; }
+    auto weight_of = [&](u32 x) -> float {                                     // RandomWalkModel::weight - deepwalk.h:67-70, node2vec.h:74-88
+        if (model == WMH_DEEPWALK) return 1.0f;
+        if (x == prev) return p.inv_p;
+        bool hit;
+        row_find(p.pool + dprev.begin, dprev.degree, x, &hit, p.shift);
+        return hit ? 1.0f : p.inv_q;
+    };
+    const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
+    u64 i = 0;
+    u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), d.degree);                       // RANDOM :72-75
+    if (p.init_strategy == WMH_INIT_BURNIN)                                                                    // :77-85
+    {
+        for (int it = 0; it < 100; it++)
+        {
+            const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), d.degree);
+            const float wn = weight_of(__ldg(nbr_ptr(p, d, cslot))), wo = weight_of(__ldg(nbr_ptr(p, d, slot)));
+            bool acc = wo < wn;
+            if (!acc) acc = unit_double(keyed_draw(p.seed, kDomSampler, cur, key_b, i++)) <= (double) wn / (double) wo;
+            if (acc) slot = cslot;
+        }
+    }
+    else if (p.init_strategy == WMH_INIT_WEIGHT)                                                               // :87-107
+    {
+        float best = weight_of(__ldg(nbr_ptr(p, d, slot)));
+        for (int it = 0; it < 20; it++)
+        {
+            const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), d.degree);
+            const float w = weight_of(__ldg(nbr_ptr(p, d, cslot)));
+            if (w > best) { best = w; slot = cslot; }
+        }
+    }
+    *init_out = __ldg(nbr_ptr(p, d, slot));
+    for (u64 k = 0; k < iters; k++)                                                                            // sample :31-46
+    {
+        const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomChain, cur, prev, 2 * k), d.degree);
+        const float wn = weight_of(__ldg(nbr_ptr(p, d, cslot))), wo = weight_of(__ldg(nbr_ptr(p, d, slot)));
+        bool acc = wo < wn;
+        if (!acc) acc = unit_double(keyed_draw(p.seed, kDomChain, cur, prev, 2 * k + 1)) <= (double) wn / (double) wo;
+        if (acc) slot = cslot;
+        counts[slot] += 1;
+    }
+}
+
 // DeepWalk in MH mode: weight == 1 (deepwalk.h:67-70) so accept() is drand() <= 1.0, always true, and the walk
 // is the proposal chain (deepwalk.h:79-87) with keyed draws.
 template <bool kRewalk>
@@ -933,6 +987,13 @@ void walks_fingerprint(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32
 {
     if (w_local == 0) return;
     fingerprint_kernel<<<div_up(w_local, 256), 256, 0, lc.stream>>>(d_walks, w_local, L, d_sum);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+void sampler_chain(const LaunchCtx& lc, const WalkParams& wp, u32 cur, u32 prev, u64 iters, u32* d_init, unsigned long long* d_counts)
+{
+    sampler_chain_kernel<<<1, 32, 0, lc.stream>>>(to_dev(wp), wp.model, cur, prev, iters, d_init, d_counts);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
 }

@@ -69,7 +69,7 @@ WHARF_HD u64 sm64(u64 z)
     return z ^ (z >> 31);
 }
 
-enum : u64 { kDomStep = 1, kDomState = 2, kDomSampler = 3 };
+enum : u64 { kDomStep = 1, kDomState = 2, kDomSampler = 3, kDomChain = 4 };
 
 WHARF_HD u64 keyed_draw(u64 seed, u64 dom, u64 a, u64 b, u64 c)
 {

@@ -197,6 +197,15 @@ class WharfMH:
         check(self._lib.wmh_affected_walks_global_device(self._h, C.c_void_p(int(d_out)), int(capacity)))
         return k
 
+    def sampler_chain(self, cur: int, prev: int, iters: int) -> tuple[int, np.ndarray]:
+        """MetropolisHastingsSampler::sample as a chain on the fixed state (cur, prev) (metropolis_hastings_sampler.h:31-46,
+        tests/sampler.cpp:86-127): (init value, counts per neighbour of cur in row order)."""
+        degree = self.degree(cur)
+        counts = np.zeros(max(degree, 1), dtype=np.uint64)
+        init = C.c_uint32()
+        check(self._lib.wmh_sampler_chain(self._h, cur, prev, iters, C.byref(init), _ptr(counts), counts.shape[0]))
+        return int(init.value), counts[:degree]
+
     def touched_vertices(self) -> np.ndarray:
         k = C.c_uint64()
         check(self._lib.wmh_touched_vertices(self._h, None, 0, C.byref(k)))

@@ -180,6 +180,15 @@ WMH_API int wmh_affected_walks(wmh_engine* e, uint64_t* ids, uint32_t* positions
 /* Device views of the same (local walk index -> use wmh_local_to_global_walk): valid until the next batch. */
 WMH_API int wmh_affected_walks_device(wmh_engine* e, const uint32_t** d_local_ids, const uint32_t** d_positions,
                                       uint64_t* count);
+/* MetropolisHastingsSampler::sample - walks/metropolis_hastings_sampler.h:31-46 - as the reference's own test drives it
+ * (tests/sampler.cpp:86-127): ONE sampler object of the fixed state (cur, prev), initialised with the engine's
+ * sampler_init_strategy (:69-108) and sampled `iters` times, its stored vertex advancing with every accepted proposal.
+ * counts[j] receives the number of samples that returned neighbour j of `cur` (capacity >= degree(cur), row order);
+ * *init_value the vertex the sampler started from.  Model, p, q and seed are the engine's; draws are keyed
+ * (seed, cur, prev, sample number), so the chain is reproducible.  For DeepWalk the weight is 1 and `prev` is unused. */
+WMH_API int wmh_sampler_chain(wmh_engine* e, uint32_t cur, uint32_t prev, uint64_t iters, uint32_t* init_value,
+                              uint64_t* counts, uint64_t capacity);
+
 /* The same ids (global, ascending) written to DEVICE memory (capacity >= the affected count): what a multi-rank caller
  * hands to its all-gather without a trip through the host.  Complete when the call returns. */
 WMH_API int wmh_affected_walks_global_device(wmh_engine* e, uint64_t* d_ids, uint64_t capacity);

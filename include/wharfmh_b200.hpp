@@ -366,8 +366,8 @@ namespace dynamic_graph_representation_learning_with_metropolis_hastings
         // :928 (device memory instead of allocator pools)
         void memory_footprint() const
         {
-            wmh_memory mem;
-            detail::check(wmh_memory_footprint(engine_, &mem));
+            wmh_memory mem{};
+            if (engine_) detail::check(wmh_memory_footprint(engine_, &mem));      // after destroy(): an empty graph, as the reference prints (tests/wharfmh.cpp:103-106)
             std::cout << "Graph: \n\t" << "Vertices: " << number_of_vertices() << ", Edges: " << number_of_edges() << std::endl;
             std::cout << "Device memory: \n\tgraph = " << mem.graph_bytes << " B (pool " << mem.graph_pool_bytes << " B), walks = " << mem.walks_bytes
                       << " B, index = " << mem.index_bytes << " B, scratch = " << mem.scratch_bytes << " B, total = " << mem.total_bytes << " B" << std::endl;

@@ -420,6 +420,34 @@ static u32 sampler_init_value(const wo_engine* e, u32 cur, u32 aux)
     return last;
 }
 
+/* MetropolisHastingsSampler::sample used as a CHAIN (metropolis_hastings_sampler.h:31-46; fixture tests/sampler.cpp:86-127):
+ * one sampler object of a fixed state (cur, aux) sampled `iters` times, its stored vertex advancing with every accepted
+ * proposal - unlike the copies generate_initial_random_walks samples from.  Starts from the init value; draws keyed
+ * (seed, DOM_CHAIN, cur, aux, 2 i) for the proposal and (..., 2 i + 1) for the acceptance test.
+ * counts[j] += 1 for every sample that returns neighbour j of cur.  Returns the init value. */
+enum { DOM_CHAIN = 4 };
+WO_API u32 wo_sampler_chain(const wo_engine* e, u32 cur, u32 aux, u64 iters, u64* counts)
+{
+    const u64 d = deg_of(e, cur);
+    if (d == 0) return WO_NO_VERTEX;
+    const u32* nb = e->col + e->row_ptr[cur];
+    const u32 init = sampler_init_value(e, cur, aux);
+    u32 last = init;
+    u64 last_slot = 0;
+    while (nb[last_slot] != last) last_slot++;
+    for (u64 i = 0; i < iters; i++)
+    {
+        const u64 cslot = irand_from(wo_keyed(e->cfg.seed, DOM_CHAIN, cur, aux, 2 * i), d);
+        const u32 cand = nb[cslot];
+        const float wn = model_weight(e, aux, cand), wo = model_weight(e, aux, last);
+        int acc = wo < wn;
+        if (!acc) acc = bits_to_unit_double(wo_keyed(e->cfg.seed, DOM_CHAIN, cur, aux, 2 * i + 1)) <= (double) wn / (double) wo;
+        if (acc) { last = cand; last_slot = cslot; }
+        counts[last_slot]++;
+    }
+    return init;
+}
+
 /* One walker, positions [start_pos, L): the loop body of wharfmh.h:294-325 (init) and :825-856 (re-walk).
  * row[start_pos] must already hold the vertex the walker stands on.  `prev` is only read in MH node2vec. */
 static u64 walk_from(wo_engine* e, u64 walk_id, u32 start_pos, u32 prev)

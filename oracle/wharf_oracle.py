@@ -90,6 +90,8 @@ def lib() -> C.CDLL:
             getattr(L, f).restype = p
         L.wo_sampler_init_value.argtypes = [p, u32, u32]
         L.wo_sampler_init_value.restype = u32
+        L.wo_sampler_chain.argtypes = [p, u32, u32, u64, p]
+        L.wo_sampler_chain.restype = u32
         L.wo_corpus_fnv1a.argtypes = [p, u64, u32]
         L.wo_corpus_fnv1a.restype = u64
         L.wo_corpus_fingerprint.argtypes = [p, u64, u32]
@@ -218,6 +220,14 @@ class Oracle:
 
     def sampler_init_value(self, cur: int, aux: int) -> int:
         return int(lib().wo_sampler_init_value(self._h, cur, aux))
+
+    def sampler_chain(self, cur: int, aux: int, iters: int) -> tuple[int, np.ndarray]:
+        """MetropolisHastingsSampler::sample as a chain on the fixed state (cur, aux): (init value, counts per neighbour slot)."""
+        row_ptr = self.csr()[0]
+        degree = int(row_ptr[cur + 1] - row_ptr[cur])
+        counts = np.zeros(max(degree, 1), dtype=np.uint64)
+        init = int(lib().wo_sampler_chain(self._h, cur, aux, iters, _ptr(counts)))
+        return init, counts[:degree]
 
 
 # ---------------------------------------------------------------------------------------------------

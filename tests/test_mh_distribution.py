@@ -89,3 +89,96 @@ def test_engine_has_the_reference_law(mh_gold, cora, wharf, index):
         shares.append(st.pop("visit_share"))
         ours.append(st)
     _compare(cfg, ours, shares)
+
+
+# ---- MetropolisHastingsSampler::sample as a chain: the reference's own fixture, tests/sampler.cpp:86-127 ----------------
+# golden.json["sampler"] holds what the UNMODIFIED reference's sampler returned (oracle/_ref `sampler` command: 4 states of the
+# six-vertex graph, 20 generator seeds x 10 000 samples each).  A chain's stored vertex advances, so its law is the model's
+# weight distribution over N(cur); the statistic is Pearson's chi-square of 20 keyed chains against the reference's pooled
+# frequencies.  Consecutive MH samples are positively correlated (a rejected proposal repeats the stored vertex), which
+# inflates the statistic by the chain's integrated autocorrelation time; the reference's own 20 runs measure that factor.
+
+def _pooled(counts_by_run, n=6):
+    tot = np.zeros(n)
+    for run in counts_by_run:
+        for k, v in run.items():
+            tot[int(k)] += v
+    return tot
+
+
+def _chi2(obs, expect_freq):
+    keep = expect_freq > 0
+    expect = expect_freq[keep] * obs.sum()
+    return float(((obs[keep] - expect) ** 2 / expect).sum()), int(keep.sum()) - 1
+
+
+def _reference_inflation(entry):
+    """Mean chi-square per degree of freedom of the reference's own single runs against its pooled frequencies."""
+    pooled = _pooled([r["counts"] for r in entry["runs"]])
+    freq = pooled / pooled.sum()
+    stats = [_chi2(_pooled([r["counts"]]), freq) for r in entry["runs"]]
+    return max(1.0, float(np.mean([c / max(dof, 1) for c, dof in stats])))
+
+
+def _chain_law_ok(entry, counts_of_seed):
+    pooled_ref = _pooled([r["counts"] for r in entry["runs"]])
+    freq = pooled_ref / pooled_ref.sum()
+    ours = np.zeros(6)
+    for seed in range(20):
+        ours += counts_of_seed(seed)
+    assert ours.sum() == 20 * entry["iters"]
+    assert ((ours > 0) == (pooled_ref > 0)).all()                      # the same support: N(cur)
+    chi2, dof = _chi2(ours, freq)
+    # both pools are samples (the reference's frequencies carry the same noise): the difference has twice the variance
+    limit = 2.0 * _reference_inflation(entry) * (dof + 6.0 * np.sqrt(2.0 * dof))
+    assert chi2 < limit, (chi2, limit, ours / ours.sum(), freq)
+
+
+@pytest.mark.parametrize("index", range(4))
+def test_sampler_chain_of_the_restatement_has_the_reference_law(golden, wo, index):
+    from conftest import SIX_EDGES, SIX_OFFSETS
+    entry = golden["sampler"][index]
+    model = wo.NODE2VEC if entry["model"] == "node2vec" else wo.DEEPWALK
+
+    def counts(seed):
+        o = wo.Oracle(6, SIX_OFFSETS, SIX_EDGES, walks_per_vertex=2, walk_length=8, model=model, p=entry["p"], q=entry["q"],
+                      deterministic=False, seed=seed)
+        init, c = o.sampler_chain(entry["cur"], entry["prev"], entry["iters"])
+        row_ptr, col = o.csr()
+        nb = col[row_ptr[entry["cur"]]:row_ptr[entry["cur"] + 1]]
+        assert init in nb.tolist() and init == o.sampler_init_value(entry["cur"], entry["prev"])
+        out = np.zeros(6)
+        out[nb] = c
+        return out
+
+    _chain_law_ok(entry, counts)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("index", range(4))
+def test_sampler_chain_on_the_device(golden, wo, wharf, index):
+    """wmh_sampler_chain: bit-exact against the restatement for every seed, and the reference's law (chi-square)."""
+    from conftest import SIX_EDGES, SIX_OFFSETS
+    entry = golden["sampler"][index]
+    model = wharf.NODE2VEC if entry["model"] == "node2vec" else wharf.DEEPWALK
+    omodel = wo.NODE2VEC if entry["model"] == "node2vec" else wo.DEEPWALK
+    nb = SIX_EDGES[int(SIX_OFFSETS[entry["cur"]]):int(SIX_OFFSETS[entry["cur"] + 1]) if entry["cur"] + 1 < 6 else len(SIX_EDGES)]
+
+    def counts(seed):
+        cfg = wharf.Config(walks_per_vertex=2, walk_length=8, random_walk_model=model, paramP=entry["p"], paramQ=entry["q"],
+                           deterministic_mode=False, seed=seed)
+        with wharf.WharfMH(6, len(SIX_EDGES), SIX_OFFSETS, SIX_EDGES, config=cfg) as e:
+            init, c = e.sampler_chain(entry["cur"], entry["prev"], entry["iters"])
+            if seed < 4:                                                # also with the interleaved row layout of a generated MH corpus
+                e.generate_initial_random_walks()
+                init2, c2 = e.sampler_chain(entry["cur"], entry["prev"], entry["iters"])
+                assert init2 == init and np.array_equal(c2, c)
+        o = wo.Oracle(6, SIX_OFFSETS, SIX_EDGES, walks_per_vertex=2, walk_length=8, model=omodel, p=entry["p"], q=entry["q"],
+                      deterministic=False, seed=seed)
+        oinit, oc = o.sampler_chain(entry["cur"], entry["prev"], entry["iters"])
+        assert init == oinit and np.array_equal(c, oc)                  # keyed draws: the same chain, bit for bit
+        out = np.zeros(6)
+        out[np.asarray(nb)] = c
+        return out
+
+    _chain_law_ok(entry, counts)

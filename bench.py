@@ -507,6 +507,10 @@ def index_vs_scan(ctx, engine, n, sizes):
     current; SCAN streams the walk matrix once."""
     torch, wharf = ctx.torch, ctx.wharf
     out = []
+    # one untimed insert + delete first: the first batches after a layout switch pay for pool growth and a compaction
+    d_warm, k_warm = make_batch_on_device(wharf, torch, max(sizes), n, 999, ctx.local_rank)
+    engine.insert_edges_batch_device(d_warm.data_ptr(), k_warm)
+    engine.delete_edges_batch_device(d_warm.data_ptr(), k_warm)
     for size in sizes:
         d_batch, k = make_batch_on_device(wharf, torch, size, n, 1000 + size, ctx.local_rank)
         row = {"batch_edges": k}

@@ -127,6 +127,7 @@ SIGNATURES = {
     "wmh_last_walk_kernel_ms": (C.c_double, [vp]),
     "wmh_last_index_ms": (C.c_double, [vp]),
     "wmh_last_search_mode": (u32, [vp]),
+    "wmh_neighbour_filter": (u32, [vp]),
     "wmh_device_walks": (vp, [vp]),
     "wmh_stream": (vp, [vp]),
     "wmh_synchronize": (i32, [vp]),

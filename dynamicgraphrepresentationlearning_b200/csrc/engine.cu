@@ -298,6 +298,7 @@ WalkParams walk_params(wmh_engine& e)
     wp.version = e.g.version.ptr;
     wp.pool_rw = e.g.tail ? e.g.pool.ptr : nullptr;
     wp.shift = e.g.tail;
+    wp.tri = e.g.tail ? e.g.tri : 0;
     wp.draw = e.draw.ptr;
     wp.walks = e.walks.ptr;
     wp.n = e.g.n;
@@ -522,14 +523,13 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
     WHARF_CUDA(cudaMemsetAsync(e.small.ptr, 0, 4, e.stream));
     graph_check_ids(lc, d_pairs, count, e.g.n, e.small.ptr);
     u32 bad = 0;
-    WHARF_CUDA(cudaMemcpyAsync(&bad, e.small.ptr, 4, cudaMemcpyDeviceToHost, e.stream));
-    WHARF_CUDA(cudaStreamSynchronize(e.stream));
-    if (bad) throw std::invalid_argument("edge batch names a vertex id >= number_of_vertices()");   // would change walk_id % n (wharfmh.h:254,368)
+    WHARF_CUDA(cudaMemcpyAsync(&bad, e.small.ptr, 4, cudaMemcpyDeviceToHost, e.stream));      // read at the first sync below: nothing is changed before
 
     // ---- graph update (graph_update_time_on_{insert,delete}, wharfmh.h:542-544 / 692-694) ----
     WHARF_CUDA(cudaEventRecord(e.ev[0], e.stream));
     PreparedBatch batch;
-    graph_prepare_batch(lc, d_pairs, count, remove_dups, e.g.n, batch, d_sorted_out);
+    graph_prepare_batch(lc, d_pairs, count, remove_dups, e.g.n, batch, d_sorted_out);                // sorts and dedups a copy; synchronises
+    if (bad) throw std::invalid_argument("edge batch names a vertex id >= number_of_vertices()");   // would change walk_id % n (wharfmh.h:254,368)
     WHARF_CUDA(cudaMemsetAsync(e.bitmap.ptr, 0, e.bitmap.bytes(), e.stream));
     if (needs_memo(e) && e.have_walks) ensure_tails(e);
     graph_apply_batch(lc, e.g, batch, is_delete, e.bitmap.ptr);
@@ -543,6 +543,16 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
     WHARF_CUDA(cudaEventRecord(e.ev[1], e.stream));
 
     // ---- walk update (walk_update_time_on_{insert,delete}, wharfmh.h:546-549 / 696-699) ----
+    // Ranks of a box: the batch emptied the sampler caches of every state whose cur is a source - on RMAT batches that is most
+    // states, because the hubs are sources - and every rank would re-derive the same init values lazily inside its re-walk.
+    // They are a pure function of the replicated graph: compute each once per box, as generate() does.  The rule uses only
+    // quantities that are equal on every rank (the ranks meet at a barrier inside).
+    bool exchanged = false;
+    if (needs_memo(e) && e.have_walks && apply_walk_updates && batch.n_sources && peer_usable(e) && e.g.last_rewritten * 4 >= e.g.m)
+    {
+        n2v_share_sampler_init(lc, walk_params(e), e.g.m, e.peer);
+        exchanged = true;
+    }
     float walk_kernel_ms = 0;
     if (e.have_walks && batch.n_sources && e.w_local)
     {
@@ -591,6 +601,7 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
     }
     WHARF_CUDA(cudaEventRecord(e.ev[2], e.stream));
     WHARF_CUDA(cudaStreamSynchronize(e.stream));
+    if (exchanged) peer_check(e);
     float graph_ms = 0, walk_ms = 0;
     WHARF_CUDA(cudaEventElapsedTime(&graph_ms, e.ev[0], e.ev[1]));
     WHARF_CUDA(cudaEventElapsedTime(&walk_ms, e.ev[1], e.ev[2]));
@@ -1331,6 +1342,7 @@ uint64_t wmh_kernel_launches(const wmh_engine* e) { return e ? e->launches : 0; 
 double wmh_last_walk_kernel_ms(const wmh_engine* e) { return e ? e->last_walk_kernel_ms : 0.0; }
 double wmh_last_index_ms(const wmh_engine* e) { return e ? e->last_index_ms : 0.0; }
 uint32_t wmh_last_search_mode(const wmh_engine* e) { return e ? e->last_search : 0u; }
+uint32_t wmh_neighbour_filter(const wmh_engine* e) { return (e && e->g.tail) ? (e->g.tri ? 2u : 1u) : 0u; }
 const uint32_t* wmh_device_walks(const wmh_engine* e) { return (e && e->have_walks) ? e->walks.ptr : nullptr; }
 void* wmh_stream(const wmh_engine* e) { return e ? (void*) e->stream : nullptr; }
 

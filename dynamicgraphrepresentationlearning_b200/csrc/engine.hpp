@@ -100,6 +100,12 @@ struct DeviceGraph
     DeviceBuffer<u32> spare;         // second pool: compaction copies into it and swaps (no allocation in steady state)
     u32 tail = 0;                    // 1: neighbour i at begin + 2 i, its aux word (sampler cache | neighbour filter) at begin + 2 i + 1
                                      //    (MH node2vec); 0: plain rows.  Doubles as the index shift of every row accessor.
+    u32 tri = 0;                     // with tail: 1 = the filter half of aux word i of row v is the TRIANGLE block of the slot v -> c
+                                     //    (Bloom block over N(v) n N(c), c = neighbour i), kept while the graph is symmetric;
+                                     //    0 = block i of row v's own neighbour filter (any graph)
+    u64 last_rewritten = 0;          // neighbours in the rows the last batch rewrote (= sampler states of those sources' rows)
+    u64 tri_stale = 0;               // edges deleted since the triangle blocks were last built: a delete leaves its bits behind
+                                     //    (a superset still proves absence, it only says "maybe" more often)
 };
 
 // One prepared edge batch (sorted, deduplicated) and what the merge learned about it.
@@ -147,6 +153,7 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int 
 // Aux tails (MH node2vec): switch the layout on (one compaction), rebuild every tail (filter set, caches empty), or
 // only empty the sampler caches.
 void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g);
+bool graph_is_symmetric(const LaunchCtx& lc, const DeviceGraph& g);   // every edge v -> c has its twin c -> v
 void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g);
 void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g);
 void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr /* n+1 */, u32* d_col /* m */);
@@ -165,6 +172,7 @@ struct WalkParams
     const u32* version = nullptr;
     u32* pool_rw = nullptr;          // the same pool, writable: aux words (MH node2vec; DeviceGraph::tail must be 1)
     u32 shift = 0;                   // DeviceGraph::tail: neighbour i of a row sits at pool[begin + (i << shift)]
+    u32 tri = 0;                     // DeviceGraph::tri: the filter halves of the aux words are triangle blocks
     const u64* draw = nullptr;       // X[wpv][L]
     u32* walks = nullptr;            // [L][W_local] position-major
     u64 n = 0;                       // global vertices

@@ -19,6 +19,7 @@
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
 
 namespace wharf
 {
@@ -173,15 +174,17 @@ __global__ void __launch_bounds__(256) merge_old_rows_kernel(const u32* __restri
             if ((u32) keys[b_lo + mid] < a) lo = mid + 1; else up = mid;
         }
         const u32 shift = (u32) (change_scan[b_lo + lo] - scan_lo);
+        u64 to;
         if (is_delete)
         {
             if (lo < b_n && (u32) keys[b_lo + lo] == a && change[b_lo + lo]) continue;     // removed
-            out[(u64) (ia - shift) << rs] = a;
+            to = (u64) (ia - shift) << rs;
         }
-        else
-        {
-            out[(u64) (ia + shift) << rs] = a;
-        }
+        else to = (u64) (ia + shift) << rs;
+        out[to] = a;
+        // aux word of a surviving slot: the filter half moves with its neighbour (triangle blocks are kept current
+        // incrementally; per-row blocks are rebuilt after the merge anyway), the sampler cache half starts empty
+        if (rs) out[to + 1] = pool[d.x + 2 * (u64) ia + 1] & 0xFFFF0000u;
     }
 }
 
@@ -194,7 +197,9 @@ __global__ void write_new_edges_kernel(const u64* __restrict__ keys, u64 k, cons
     if (i >= k || !change[i]) return;
     const u32 j = upper_segment_u64(slice, (u32) n_sources + 1, i);
     const u64 within = change_scan[i] - change_scan[slice[j]];
-    pool[pool_base + alloc_scan[j] + ((rank[i] + within) << rs)] = (u32) keys[i];
+    const u64 to = pool_base + alloc_scan[j] + ((rank[i] + within) << rs);
+    pool[to] = (u32) keys[i];
+    if (rs) pool[to + 1] = 0;                                     // aux word of a new slot: empty cache, empty filter block
 }
 
 // Repoint the rows, bump the sampler-manager generation (wharfmh.h:504 -> :539) and mark the touched bitmap.
@@ -273,6 +278,253 @@ __global__ void __launch_bounds__(256) aux_invalidate_kernel(const RowDesc* __re
     }
 }
 
+// ---- triangle blocks (MH node2vec on a symmetric graph) -----------------------------------------------------
+// Filter half of aux word i of row v, c = neighbour i:  OR over w in N(v) n N(c) of filter_bits(filter_hash(w)).
+// node2vec asks "is the proposal c a neighbour of prev" for a walker standing on v that came from prev (node2vec.h:
+// 74-88,112-119).  prev is a neighbour of v, and on a symmetric graph c in N(prev) <=> prev in N(c) <=> prev in N(v) n N(c):
+// the block of the slot v -> c, which arrives with the load that picks c, answers it (94 % of the proposals are no
+// neighbour of prev and the sets are nearly empty: mean 0.28 members at scale-20).  A block is a Bloom filter: extra bits
+// only turn a proof of absence into a "maybe", which the walk kernel resolves with the exact search.
+constexpr u32 kTriChunk = 128;       // slots of one row handled by one warp (four 8-lane groups x 32 slots)
+constexpr u32 kTriHeavy = 2048;      // slots whose smaller row is longer than this go to a block of their own
+
+// N(v) n N(c) as a Bloom block, by the lanes `sub` of `lanes` cooperating lanes: every member of the shorter row is
+// searched in the longer one.  The caller ORs the partial results.
+__device__ __forceinline__ u32 tri_block_partial(const u32* __restrict__ pool, uint2 dv, uint2 dc, u32 sub, u32 lanes)
+{
+    const uint2 small = dv.y <= dc.y ? dv : dc, large = dv.y <= dc.y ? dc : dv;
+    u32 bits = 0;
+    for (u32 k = sub; k < small.y; k += lanes)
+    {
+        const u32 x = __ldg(pool + small.x + 2 * (u64) k);
+        const u32 r = lower_bound_row(pool + large.x, large.y, x, 1);
+        if (r < large.y && __ldg(pool + large.x + 2 * (u64) r) == x) bits |= filter_bits(filter_hash(x));
+    }
+    return bits;
+}
+
+__device__ __forceinline__ void tri_store(u32* __restrict__ pool, uint2 dv, u32 i, u32 bits)
+{
+    reinterpret_cast<unsigned short*>(pool + dv.x + 2 * (u64) i + 1)[1] = (unsigned short) bits;      // high half only
+}
+
+struct TriChunksOf
+{
+    const RowDesc* desc;
+    const u32* rows;      // nullptr: every vertex
+    u64 count;
+    __device__ u64 operator()(u64 j) const
+    {
+        if (j >= count) return 0;
+        const u32 v = rows ? rows[j] : (u32) j;
+        return (desc[v].degree + kTriChunk - 1) / kTriChunk;
+    }
+};
+
+// One warp per chunk of kTriChunk slots of a row (rows == nullptr: all rows; else the listed rows).  mirror: also store the
+// block into the slot c -> v (the same set on a symmetric graph) - used when only some rows are rebuilt.
+__global__ void __launch_bounds__(256) tri_build_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ rows,
+                                                        u64 n_rows, const u64* __restrict__ chunk_scan, u64 n_chunks, bool mirror,
+                                                        uint2* __restrict__ heavy, u32* __restrict__ heavy_count, u32 heavy_capacity)
+{
+    const u64 chunk = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (chunk >= n_chunks) return;
+    const u32 lane = threadIdx.x & 31, sub = lane & 7, group = lane >> 3;
+    const u32 j = upper_segment_u64(chunk_scan, (u32) n_rows + 1, chunk);
+    const u32 v = rows ? rows[j] : j;
+    const uint2 dv = reinterpret_cast<const uint2*>(desc)[v];
+    const u32 first = (u32) (chunk - chunk_scan[j]) * kTriChunk;
+    const u32 last = min(dv.y, first + kTriChunk);
+    for (u32 i0 = first; i0 < last; i0 += 4)                      // uniform trip count: the shuffles below need the whole warp
+    {
+        const u32 i = i0 + group;
+        const bool has = i < last;
+        u32 c = 0;
+        uint2 dc = make_uint2(0, 0);
+        if (has)
+        {
+            c = __ldg(pool + dv.x + 2 * (u64) i);
+            dc = reinterpret_cast<const uint2*>(desc)[c];
+        }
+        const bool is_heavy = has && min(dv.y, dc.y) > kTriHeavy;
+        u32 bits = (has && !is_heavy) ? tri_block_partial(pool, dv, dc, sub, 8) : 0u;
+        bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
+        bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
+        bits |= __shfl_xor_sync(0xffffffffu, bits, 4);
+        if (has && sub == 0)
+        {
+            if (is_heavy)
+            {
+                const u32 at = atomicAdd(heavy_count, 1u);
+                if (at < heavy_capacity) heavy[at] = make_uint2(v, i);
+                else tri_store(pool, dv, i, 0xFFFFu);              // list full: "maybe" for every query, the exact search decides
+            }
+            else
+            {
+                tri_store(pool, dv, i, bits);
+                if (mirror)
+                {
+                    const u32 r = lower_bound_row(pool + dc.x, dc.y, v, 1);
+                    if (r < dc.y && pool[dc.x + 2 * (u64) r] == v) tri_store(pool, dc, r, bits);
+                }
+            }
+        }
+    }
+}
+
+// One block per heavy slot (both rows long: hub - hub edges).
+__global__ void __launch_bounds__(256) tri_heavy_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const uint2* __restrict__ heavy,
+                                                        const u32* __restrict__ heavy_count, u32 heavy_capacity, bool mirror)
+{
+    __shared__ u32 s_bits;
+    const u32 count = min(*heavy_count, heavy_capacity);
+    for (u32 h = blockIdx.x; h < count; h += gridDim.x)
+    {
+        const uint2 item = heavy[h];
+        const uint2 dv = reinterpret_cast<const uint2*>(desc)[item.x];
+        const u32 c = pool[dv.x + 2 * (u64) item.y];
+        const uint2 dc = reinterpret_cast<const uint2*>(desc)[c];
+        if (threadIdx.x == 0) s_bits = 0;
+        __syncthreads();
+        const u32 bits = tri_block_partial(pool, dv, dc, threadIdx.x, 256);
+        if (bits) atomicOr(&s_bits, bits);
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            tri_store(pool, dv, item.y, s_bits);
+            if (mirror)
+            {
+                const u32 r = lower_bound_row(pool + dc.x, dc.y, item.x, 1);
+                if (r < dc.y && pool[dc.x + 2 * (u64) r] == item.x) tri_store(pool, dc, r, s_bits);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// Insert batch, after the merge: one 8-lane group per batch edge (a, b) that is new to the row of a.  With I = N(a) n N(b)
+// in the NEW graph: the slot a -> b gets the block of I; b joined N(a), so for every w in I the set of the slots a -> w and
+// w -> a gained b.  (The twin key (b, a) of a symmetric batch does the same with the roles swapped.)  ORs are idempotent,
+// so edges of one batch that close triangles with each other need no ordering.  Hub - hub edges go to the heavy list.
+__global__ void __launch_bounds__(256) tri_insert_kernel(const u64* __restrict__ keys, u64 k, const u32* __restrict__ change,
+                                                         const RowDesc* __restrict__ desc, u32* __restrict__ pool,
+                                                         uint2* __restrict__ heavy, u32* __restrict__ heavy_count, u32 heavy_capacity)
+{
+    const u64 item = ((u64) blockIdx.x * 256 + threadIdx.x) >> 3;
+    const u32 sub = threadIdx.x & 7;
+    const bool has = item < k && change[item];
+    u32 a = 0, b = 0;
+    uint2 da = make_uint2(0, 0), db = make_uint2(0, 0);
+    if (has)
+    {
+        a = (u32) (keys[item] >> 32);
+        b = (u32) keys[item];
+        da = reinterpret_cast<const uint2*>(desc)[a];
+        db = reinterpret_cast<const uint2*>(desc)[b];
+    }
+    const bool is_heavy = has && min(da.y, db.y) > kTriHeavy;
+    u32 bits = 0;
+    if (has && !is_heavy)
+    {
+        const bool a_small = da.y <= db.y;
+        const uint2 small = a_small ? da : db, large = a_small ? db : da;
+        const u32 bits_b = filter_bits(filter_hash(b)) << 16;
+        for (u32 q = sub; q < small.y; q += 8)
+        {
+            const u32 w = __ldg(pool + small.x + 2 * (u64) q);
+            const u32 r = lower_bound_row(pool + large.x, large.y, w, 1);
+            if (r >= large.y || __ldg(pool + large.x + 2 * (u64) r) != w) continue;
+            bits |= filter_bits(filter_hash(w));
+            atomicOr(pool + da.x + 2 * (u64) (a_small ? q : r) + 1, bits_b);                     // slot a -> w
+            const uint2 dw = reinterpret_cast<const uint2*>(desc)[w];
+            const u32 ra = lower_bound_row(pool + dw.x, dw.y, a, 1);
+            if (ra < dw.y && pool[dw.x + 2 * (u64) ra] == a) atomicOr(pool + dw.x + 2 * (u64) ra + 1, bits_b);   // slot w -> a
+        }
+    }
+    bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
+    bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
+    bits |= __shfl_xor_sync(0xffffffffu, bits, 4);
+    if (has && sub == 0)
+    {
+        const u32 rb = lower_bound_row(pool + da.x, da.y, b, 1);                                    // slot a -> b
+        if (is_heavy)
+        {
+            const u32 at = atomicAdd(heavy_count, 1u);
+            if (at < heavy_capacity) heavy[at] = make_uint2(a, rb);
+            else if (rb < da.y) atomicOr(pool + da.x + 2 * (u64) rb + 1, 0xFFFF0000u);   // list full: the row of a answers "maybe"
+        }
+        else if (bits && rb < da.y) atomicOr(pool + da.x + 2 * (u64) rb + 1, bits << 16);
+    }
+}
+
+// Heavy inserted edges: block per edge; slot = (a, index of b in the row of a).
+__global__ void __launch_bounds__(256) tri_insert_heavy_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const uint2* __restrict__ heavy,
+                                                               const u32* __restrict__ heavy_count, u32 heavy_capacity)
+{
+    __shared__ u32 s_bits;
+    const u32 count = min(*heavy_count, heavy_capacity);
+    for (u32 h = blockIdx.x; h < count; h += gridDim.x)
+    {
+        const u32 a = heavy[h].x, rb = heavy[h].y;
+        const uint2 da = reinterpret_cast<const uint2*>(desc)[a];
+        const u32 b = pool[da.x + 2 * (u64) rb];
+        const uint2 db = reinterpret_cast<const uint2*>(desc)[b];
+        if (threadIdx.x == 0) s_bits = 0;
+        __syncthreads();
+        const bool a_small = da.y <= db.y;
+        const uint2 small = a_small ? da : db, large = a_small ? db : da;
+        const u32 bits_b = filter_bits(filter_hash(b)) << 16;
+        u32 bits = 0;
+        for (u32 q = threadIdx.x; q < small.y; q += 256)
+        {
+            const u32 w = __ldg(pool + small.x + 2 * (u64) q);
+            const u32 r = lower_bound_row(pool + large.x, large.y, w, 1);
+            if (r >= large.y || __ldg(pool + large.x + 2 * (u64) r) != w) continue;
+            bits |= filter_bits(filter_hash(w));
+            atomicOr(pool + da.x + 2 * (u64) (a_small ? q : r) + 1, bits_b);
+            const uint2 dw = reinterpret_cast<const uint2*>(desc)[w];
+            const u32 ra = lower_bound_row(pool + dw.x, dw.y, a, 1);
+            if (ra < dw.y && pool[dw.x + 2 * (u64) ra] == a) atomicOr(pool + dw.x + 2 * (u64) ra + 1, bits_b);
+        }
+        if (bits) atomicOr(&s_bits, bits);
+        __syncthreads();
+        if (threadIdx.x == 0 && s_bits) atomicOr(pool + da.x + 2 * (u64) rb + 1, s_bits << 16);
+        __syncthreads();
+    }
+}
+
+// flag |= 1 when some edge v -> c has no twin c -> v (one thread per slot of a chunked row walk is overkill: 8 lanes per row).
+__global__ void __launch_bounds__(256) symmetric_graph_kernel(const RowDesc* __restrict__ desc, u64 n, const u32* __restrict__ pool, u32 rs, u32* __restrict__ flag)
+{
+    const u64 g = ((u64) blockIdx.x * 256 + threadIdx.x) >> 3;
+    const u32 sub = threadIdx.x & 7;
+    if (g >= n) return;
+    const uint2 dv = reinterpret_cast<const uint2*>(desc)[g];
+    for (u32 i = sub; i < dv.y; i += 8)
+    {
+        const u32 c = pool[dv.x + ((u64) i << rs)];
+        const uint2 dc = reinterpret_cast<const uint2*>(desc)[c];
+        const u32 r = lower_bound_row(pool + dc.x, dc.y, (u32) g, rs);
+        if (r >= dc.y || pool[dc.x + ((u64) r << rs)] != (u32) g) { *flag = 1; return; }
+    }
+}
+
+// flag |= 1 when some batch key (s, d) has no twin (d, s) in the same (sorted, unique) batch.
+__global__ void symmetric_batch_kernel(const u64* __restrict__ keys, u64 k, u32* __restrict__ flag)
+{
+    const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k) return;
+    const u64 key = keys[i];
+    const u64 twin = (key << 32) | (key >> 32);
+    u64 lo = 0, hi = k;
+    while (lo < hi)
+    {
+        const u64 mid = (lo + hi) >> 1;
+        if (keys[mid] < twin) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= k || keys[lo] != twin) *flag = 1;
+}
+
 // ---- row copy (compaction / export) ---------------------------------------------------------------
 __global__ void degrees_kernel(const RowDesc* __restrict__ desc, u64 n, u32 row_words, u64* __restrict__ deg)
 {
@@ -291,7 +543,11 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(const RowDesc* __restric
     const uint2 d = reinterpret_cast<const uint2*>(desc)[g];
     if (d.y > kBigRow) return;
     const u64 o = dst_offset[g];
-    for (u32 i = sub; i < d.y; i += 8) dst[o + ((u64) i << ds)] = pool[d.x + ((u64) i << ss)];
+    for (u32 i = sub; i < d.y; i += 8)
+    {
+        dst[o + ((u64) i << ds)] = pool[d.x + ((u64) i << ss)];
+        if (ds) dst[o + 2 * (u64) i + 1] = ss ? pool[d.x + 2 * (u64) i + 1] & 0xFFFF0000u : 0u;    // filter half travels, cache half empties
+    }
 }
 
 struct IsBigRow
@@ -307,7 +563,11 @@ __global__ void __launch_bounds__(256) copy_big_rows_kernel(const u32* __restric
     const u32 v = rows[blockIdx.x];
     const uint2 d = reinterpret_cast<const uint2*>(desc)[v];
     const u64 o = dst_offset[v];
-    for (u32 i = threadIdx.x; i < d.y; i += 256) dst[o + ((u64) i << ds)] = pool[d.x + ((u64) i << ss)];
+    for (u32 i = threadIdx.x; i < d.y; i += 256)
+    {
+        dst[o + ((u64) i << ds)] = pool[d.x + ((u64) i << ss)];
+        if (ds) dst[o + 2 * (u64) i + 1] = ss ? pool[d.x + 2 * (u64) i + 1] & 0xFFFF0000u : 0u;
+    }
 }
 
 __global__ void repoint_kernel(RowDesc* __restrict__ desc, u64 n, const u64* __restrict__ new_begin)
@@ -554,14 +814,78 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int 
     WHARF_CUDA(cudaGetLastError());
     std::swap(g.pool, g.spare);
     g.pool_used = live;
-    if (g.tail) graph_aux_rebuild(lc, g);
+    if (g.tail && src_shift == 0)
+    {
+        // rows just moved into the interleaved layout (aux words zero): triangle blocks while the graph is symmetric
+        // (WHARF_TRI=0 keeps per-row blocks: A/B measurements), per-row blocks otherwise
+        const char* env = std::getenv("WHARF_TRI");
+        g.tri = (!(env && std::atoi(env) == 0) && graph_is_symmetric(lc, g)) ? 1u : 0u;
+        g.tri_stale = 0;
+        graph_aux_rebuild(lc, g);
+    }
+    else if (g.tail && !g.tri) graph_aux_rebuild(lc, g);        // triangle blocks travelled with their slots (copy_rows_kernel)
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
     tr.mark("compact: repoint+aux");
 }
 
+bool graph_is_symmetric(const LaunchCtx& lc, const DeviceGraph& g)
+{
+    if (g.n == 0) return true;
+    Scratch<u32> flag(lc.stream, 1);
+    WHARF_CUDA(cudaMemsetAsync(flag.ptr, 0, 4, lc.stream));
+    symmetric_graph_kernel<<<div_up(g.n * 8, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr, g.tail, flag.ptr);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+    u32 bad = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&bad, flag.ptr, 4, cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
+    return bad == 0;
+}
+
+namespace
+{
+constexpr u32 kTriHeavyCapacity = 1u << 22;      // hub - hub slots parked for the block-per-slot kernel (32 MB of scratch)
+
+// Triangle blocks of every slot of the listed rows (rows == nullptr: all rows).  mirror: the twin slots c -> v get the same
+// block (partial rebuilds).
+void tri_build(const LaunchCtx& lc, DeviceGraph& g, const u32* d_rows, u64 n_rows, bool mirror)
+{
+    if (n_rows == 0) return;
+    Scratch<u64> chunk_scan(lc.stream, n_rows + 1);
+    {
+        cub::CountingInputIterator<u64> iota(0);
+        cub::TransformInputIterator<u64, TriChunksOf, cub::CountingInputIterator<u64>> chunks(iota, TriChunksOf{g.desc.ptr, d_rows, n_rows});
+        size_t temp_bytes = 0;
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, chunks, chunk_scan.ptr, (i64) (n_rows + 1), lc.stream));
+        Scratch<u8> temp(lc.stream, temp_bytes);
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(temp.ptr, temp_bytes, chunks, chunk_scan.ptr, (i64) (n_rows + 1), lc.stream));
+        lc.count_lib();
+    }
+    u64 n_chunks = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&n_chunks, chunk_scan.ptr + n_rows, 8, cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
+    if (n_chunks == 0) return;
+    Scratch<uint2> heavy(lc.stream, kTriHeavyCapacity);
+    Scratch<u32> heavy_count(lc.stream, 1);
+    WHARF_CUDA(cudaMemsetAsync(heavy_count.ptr, 0, 4, lc.stream));
+    tri_build_kernel<<<div_up(n_chunks * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, d_rows, n_rows, chunk_scan.ptr, n_chunks, mirror,
+                                                                        heavy.ptr, heavy_count.ptr, kTriHeavyCapacity);
+    tri_heavy_kernel<<<lc.sm_count * 4, 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, heavy.ptr, heavy_count.ptr, kTriHeavyCapacity, mirror);
+    lc.count(2);
+    WHARF_CUDA(cudaGetLastError());
+}
+}  // namespace
+
 void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g)
 {
     if (!g.tail || g.n == 0) return;
+    if (g.tri)
+    {
+        graph_aux_clear_caches(lc, g);                            // cache halves empty; the build overwrites every filter half
+        tri_build(lc, g, nullptr, g.n, false);
+        g.tri_stale = 0;
+        return;
+    }
     aux_build_all_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
@@ -605,12 +929,23 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     exclusive_sum(lc, alloc.ptr, alloc_scan.ptr, ns + 1);
     exclusive_sum(lc, chunks.ptr, chunk_scan.ptr, ns + 1);
 
+    Scratch<u32> asym(lc.stream, 1);
+    u32 batch_asymmetric = 0;
+    if (g.tail && g.tri)
+    {
+        // triangle blocks answer "x in N(prev)" through "prev in N(x)": they stand only while every batch keeps the graph symmetric
+        WHARF_CUDA(cudaMemsetAsync(asym.ptr, 0, 4, lc.stream));
+        symmetric_batch_kernel<<<div_up(k, 256), 256, 0, lc.stream>>>(b.keys.ptr, k, asym.ptr);
+        lc.count();
+        WHARF_CUDA(cudaMemcpyAsync(&batch_asymmetric, asym.ptr, 4, cudaMemcpyDeviceToHost, lc.stream));
+    }
     u64 totals[3];   // appended pool words, chunks, changed edges
     WHARF_CUDA(cudaMemcpyAsync(&totals[0], alloc_scan.ptr + ns, 8, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaMemcpyAsync(&totals[1], chunk_scan.ptr + ns, 8, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaMemcpyAsync(&totals[2], change_scan.ptr + k, 8, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
     const u64 total = totals[0], n_chunks = totals[1], changed = totals[2];
+    g.last_rewritten = total >> g.tail;
     tr.mark("apply: locate+plan");
 
     const bool compacted = g.pool_used + total > g.pool.count;
@@ -638,7 +973,39 @@ void graph_apply_batch(const LaunchCtx& lc, DeviceGraph& g, const PreparedBatch&
     tr.mark("apply: merge+write+commit");
     g.pool_used += total;
     g.m = is_delete ? g.m - changed : g.m + changed;
-    if (g.tail)
+    if (g.tail && g.tri && batch_asymmetric)
+    {
+        // a directed batch: back to per-row blocks for good (every aux word rebuilt: filters set, caches empty)
+        g.tri = 0;
+        graph_aux_rebuild(lc, g);
+        tr.mark("apply: aux tails (triangle blocks dropped)");
+    }
+    else if (g.tail && g.tri)
+    {
+        // the merge carried the blocks of the surviving slots and left new slots empty.  Inserts: one intersection per new
+        // edge ORs the bits it adds.  Deletes leave their bits behind (a superset still proves absence); once a quarter of
+        // the edges' worth has been deleted the blocks are rebuilt.  Caches whose cur is a source: emptied.
+        if (!is_delete)
+        {
+            Scratch<uint2> heavy(lc.stream, kTriHeavyCapacity);
+            Scratch<u32> heavy_count(lc.stream, 1);
+            WHARF_CUDA(cudaMemsetAsync(heavy_count.ptr, 0, 4, lc.stream));
+            tri_insert_kernel<<<div_up(k * 8, 256), 256, 0, lc.stream>>>(b.keys.ptr, k, change.ptr, g.desc.ptr, g.pool.ptr, heavy.ptr, heavy_count.ptr,
+                                                                         kTriHeavyCapacity);
+            tri_insert_heavy_kernel<<<lc.sm_count * 2, 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, heavy.ptr, heavy_count.ptr, kTriHeavyCapacity);
+            lc.count(2);
+        }
+        else g.tri_stale += changed;
+        if (g.tri_stale > g.m / 4 + 1024) graph_aux_rebuild(lc, g);
+        else
+        {
+            aux_invalidate_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr, d_touched_bitmap);
+            lc.count();
+        }
+        WHARF_CUDA(cudaGetLastError());
+        tr.mark("apply: aux tails (triangle blocks)");
+    }
+    else if (g.tail)
     {
         // fresh rows: filter set, caches empty; every other cache whose cur is a source: emptied
         aux_build_sources_kernel<<<div_up(ns * 32, 256), 256, 0, lc.stream>>>(b.sources.ptr, ns, g.desc.ptr, g.pool.ptr);

@@ -39,6 +39,8 @@ struct DevWalkParams
     ShardMap map;                     // local walk -> (replica, start vertex)
     u32 L;
     u32 shift;                        // neighbour i of a row sits at pool[begin + (i << shift)] (1: interleaved with aux words)
+    u32 coop_search;                  // 1: membership searches in rows of >= kCoopMin neighbours are done by the whole warp
+    u32 tri;                          // 1: the filter half of an aux word is the TRIANGLE block of its slot (kernels_graph.cu); 0: per-row blocks
     u32 init_strategy;
     float inv_p, inv_q;
     u64 seed;
@@ -239,17 +241,64 @@ __device__ __forceinline__ u32 row_find(const u32* __restrict__ row, u32 n, u32 
     return base;
 }
 
-// Node2Vec::weight as a class - walks/models/node2vec.h:74-88; state = (cur, prev), dprev = row of prev.
-__device__ __forceinline__ u32 n2v_class(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x)
+// Node2Vec::weight as a class - walks/models/node2vec.h:74-88; state = (cur, prev), dprev = row of prev, x = a neighbour
+// of cur and x_aux the aux word of the slot cur -> x (it came with the 8-byte load that fetched x).
+// Triangle blocks (p.tri; symmetric graphs): the filter half of x_aux is a Bloom block over N(cur) n N(x) hashed by member.
+// prev is a neighbour of cur (the walker came from there), so a clear bit of hash(prev) proves prev is no neighbour of x,
+// i.e. x is no neighbour of prev - decided by the load that was made anyway, without touching the row of prev.  Only a
+// "maybe" (true common neighbours and ~1.5 % false positives) goes on to the exact search (node2vec.h:112-119).
+// Per-row blocks (directed graphs): one 16-bit block of the row of prev, hashed by x, is loaded instead.
+constexpr u32 kClassPending = 3;     // the filter could not rule x out: the exact search decides
+
+__device__ __forceinline__ u32 n2v_prefilter(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x, u32 x_aux)
 {
     if (x == prev) return kClassReturn;
     if (dprev.degree == 0) return kClassFar;
-    const u32 h = filter_hash(x);
-    const u32 need = filter_bits(h);
-    if (((__ldcg(aux_ptr(p, dprev, filter_block(h, dprev.degree))) >> 16) & need) != need) return kClassFar;   // proven absent
+    if (p.tri)
+    {
+        const u32 need = filter_bits(filter_hash(prev));
+        if (((x_aux >> 16) & need) != need) return kClassFar;                                               // proven absent
+    }
+    else
+    {
+        const u32 h = filter_hash(x);
+        const u32 need = filter_bits(h);
+        if (((__ldcg(aux_ptr(p, dprev, filter_block(h, dprev.degree))) >> 16) & need) != need) return kClassFar;   // proven absent
+    }
+    return kClassPending;
+}
+
+__device__ __forceinline__ u32 n2v_class(const DevWalkParams& p, u32 prev, RowDesc dprev, u32 x, u32 x_aux)
+{
+    const u32 cls = n2v_prefilter(p, prev, dprev, x, x_aux);
+    if (cls != kClassPending) return cls;
     bool hit;
     row_find(p.pool + dprev.begin, dprev.degree, x, &hit, p.shift);
     return hit ? kClassNeighbour : kClassFar;
+}
+
+// std::binary_search(N(prev), x) (node2vec.h:112-119) by the WHOLE warp: 32 probes per round cut the range 33-fold, so a
+// row of 10^5 neighbours takes 3 rounds + one final 32-wide compare instead of 17 dependent loads of one lane.  Every lane
+// calls it with the same arguments.  Used for rows of kCoopMin neighbours and more when WHARF_COOP_SEARCH=1 (A/B:
+// profiles/r02*_coop_search*.txt); the queries of a warp are then served one after the other.
+constexpr u32 kCoopMin = 1024;
+__device__ __forceinline__ bool row_find_warp(const u32* __restrict__ row, u32 n, u32 key, u32 shift, u32 lane)
+{
+    u32 lo = 0, hi = n;                                   // the element equal to key, if any, sits in [lo, hi)
+    while (hi - lo > 32)
+    {
+        const u32 span = hi - lo;
+        const u32 pos = lo + (u32) (((u64) (lane + 1) * span) / 33);            // lo < pos < hi
+        const bool le = __ldg(row + ((u64) pos << shift)) <= key;
+        const u32 k = __popc(__ballot_sync(0xffffffffu, le));                   // ascending row: the first k probes are <= key
+        const u32 nlo = k ? lo + (u32) (((u64) k * span) / 33) : lo;
+        const u32 nhi = k < 32 ? lo + (u32) (((u64) (k + 1) * span) / 33) : hi;
+        lo = nlo;
+        hi = nhi;
+    }
+    const u32 pos = lo + lane;
+    const bool eq = pos < hi && __ldg(row + ((u64) pos << shift)) == key;
+    return __any_sync(0xffffffffu, eq);
 }
 
 // MetropolisHastingsSampler::accept - walks/metropolis_hastings_sampler.h:118-122.
@@ -267,14 +316,16 @@ __device__ InitValue n2v_init_serial(const DevWalkParams& p, u32 cur, RowDesc dc
     u64 i = 0;
     u32 draw = 0;
     u32 slot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);                 // RANDOM :72-75
-    u32 cls = n2v_class(p, prev, dprev, __ldg(nbr_ptr(p, dcur, slot)));
+    uint2 pair = load_pair(p, dcur, slot);
+    u32 cls = n2v_class(p, prev, dprev, pair.x, pair.y);
     if (p.init_strategy == WMH_INIT_BURNIN)                                                                // :77-85
     {
         for (int it = 0; it < 100; it++)
         {
             const u32 cdraw = (u32) i;
             const u32 cslot = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, i++), dcur.degree);
-            const u32 ccls = n2v_class(p, prev, dprev, __ldg(nbr_ptr(p, dcur, cslot)));
+            pair = load_pair(p, dcur, cslot);
+            const u32 ccls = n2v_class(p, prev, dprev, pair.x, pair.y);
             const float wn = class_weight(p, ccls), wo = class_weight(p, cls);
             bool acc = wo < wn;
             if (!acc) acc = unit_double(keyed_draw(p.seed, kDomSampler, cur, key_b, i++)) <= (double) wn / (double) wo;
@@ -299,13 +350,29 @@ __device__ __forceinline__ InitValue n2v_init_weight_group(const DevWalkParams& 
         u32 slot[3], x[3], fh[3], fw[3];
 #pragma unroll
         for (u32 k = 0; k < 3; k++) slot[k] = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, sub + 8 * k), dcur.degree);
-#pragma unroll
-        for (u32 k = 0; k < 3; k++) x[k] = __ldg(nbr_ptr(p, dcur, slot[k]));
-#pragma unroll
-        for (u32 k = 0; k < 3; k++)
+        if (p.tri)
         {
-            fh[k] = filter_hash(x[k]);
-            fw[k] = dprev.degree ? __ldcg(aux_ptr(p, dprev, filter_block(fh[k], dprev.degree))) >> 16 : 0u;
+            // triangle blocks: the filter word of proposal x is the aux word of the slot cur -> x, tested with hash(prev)
+            const u32 hp = filter_hash(prev);
+#pragma unroll
+            for (u32 k = 0; k < 3; k++)
+            {
+                const uint2 pair = load_pair(p, dcur, slot[k]);
+                x[k] = pair.x;
+                fw[k] = pair.y >> 16;
+                fh[k] = hp;
+            }
+        }
+        else
+        {
+#pragma unroll
+            for (u32 k = 0; k < 3; k++) x[k] = __ldg(nbr_ptr(p, dcur, slot[k]));
+#pragma unroll
+            for (u32 k = 0; k < 3; k++)
+            {
+                fh[k] = filter_hash(x[k]);
+                fw[k] = dprev.degree ? __ldcg(aux_ptr(p, dprev, filter_block(fh[k], dprev.degree))) >> 16 : 0u;
+            }
         }
         // classes: return / far are decided by the filter alone; the few proposals the filter cannot rule out (common
         // neighbours and 2.5 % false positives) are searched afterwards, one per lane and trip - the search is a
@@ -415,7 +482,26 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
             cand = pair.x;
             cand_aux = pair.y;
             dcand = load_desc(p.desc, cand);
-            cls_new = n2v_class(p, prev, dprev, cand);
+            cls_new = n2v_prefilter(p, prev, dprev, cand, cand_aux);
+            if (cls_new == kClassPending && !(p.coop_search && dprev.degree >= kCoopMin))
+            {
+                bool hit;                                   // per-thread search: 32 independent chains per warp
+                row_find(p.pool + dprev.begin, dprev.degree, cand, &hit, p.shift);
+                cls_new = hit ? kClassNeighbour : kClassFar;
+            }
+        }
+        if (p.coop_search)
+        {
+            u32 pending = __ballot_sync(0xffffffffu, step && cls_new == kClassPending);     // long rows, one query at a time
+            while (pending)
+            {
+                const int src = __ffs(pending) - 1;
+                pending &= pending - 1;
+                const u32 b = __shfl_sync(0xffffffffu, dprev.begin, src), nn = __shfl_sync(0xffffffffu, dprev.degree, src);
+                const u32 key = __shfl_sync(0xffffffffu, cand, src);
+                const bool hit = row_find_warp(p.pool + b, nn, key, p.shift, lane);
+                if ((int) lane == src) cls_new = hit ? kClassNeighbour : kClassFar;
+            }
         }
         const bool need = step && !(cache & kCacheValid);
         InitValue iv{kClassFar, 0, 0};
@@ -857,6 +943,11 @@ DevWalkParams to_dev(const WalkParams& wp)
     p.n = wp.n; p.w_local = wp.w_local; p.map = wp.map; p.L = wp.L;
     p.init_strategy = wp.init_strategy;
     p.shift = wp.shift;
+    p.tri = wp.tri;
+    {
+        const char* coop = std::getenv("WHARF_COOP_SEARCH");
+        p.coop_search = coop && std::atoi(coop) != 0;
+    }
     p.inv_p = 1 / wp.p;                                                 // node2vec.h:78
     p.inv_q = 1 / wp.q;                                                 // node2vec.h:86
     p.seed = wp.seed;

@@ -338,6 +338,10 @@ class WharfMH:
         """SEARCH_INDEX / SEARCH_SCAN as taken by the last batch (0: none)."""
         return int(self._lib.wmh_last_search_mode(self._h))
 
+    def neighbour_filter(self) -> int:
+        """0: no aux words yet, 1: per-row blocks, 2: triangle blocks (wmh_neighbour_filter)."""
+        return int(self._lib.wmh_neighbour_filter(self._h))
+
     def device_walks_ptr(self) -> int:
         return int(self._lib.wmh_device_walks(self._h) or 0)
 

@@ -279,6 +279,11 @@ WMH_API double   wmh_last_walk_kernel_ms(const wmh_engine* e);
 WMH_API double   wmh_last_index_ms(const wmh_engine* e);
 /* How the last batch found its affected walks: WMH_SEARCH_INDEX or WMH_SEARCH_SCAN as TAKEN (0: no search ran). */
 WMH_API uint32_t wmh_last_search_mode(const wmh_engine* e);
+/* How node2vec's "is the proposal a neighbour of prev" test (walks/models/node2vec.h:74-88,112-119) is pre-filtered in
+ * Metropolis-Hastings mode: 0 = no aux words yet (no MH node2vec corpus so far), 1 = per-row Bloom blocks (any graph),
+ * 2 = triangle blocks keyed on the traversed edge (symmetric graph and symmetric batches only; a directed batch drops
+ * the engine back to 1).  The filter only prunes exact searches: corpora are identical in every mode. */
+WMH_API uint32_t wmh_neighbour_filter(const wmh_engine* e);
 /* Raw device pointers for zero-copy consumers (position-major walk matrix [L][local_walks]). */
 WMH_API const uint32_t* wmh_device_walks(const wmh_engine* e);
 WMH_API void*    wmh_stream(const wmh_engine* e);                        /* cudaStream_t */

@@ -147,3 +147,51 @@ def test_insert_then_delete_round_trip(wharf, graph):
         have = (np.repeat(np.arange(graph["n"], dtype=np.int64), np.diff(rp.astype(np.int64))) << 32) | col.astype(np.int64)
         assert np.array_equal(have, want), "adjacency after insert + delete is not original minus batch"
         check_walks_are_valid(graph, e, keys=torch.from_numpy(have).cuda(), degree=torch.from_numpy(np.diff(rp.astype(np.int64))).cuda())
+
+
+def test_walk_keys_beyond_32_bits_equal_the_oracle(wharf):
+    """walk_id * walk_length + position is a uint32_t in the reference (walks/inverted_index.h:14,76; graph/wharfmh.h:316) and
+    wraps beyond 2^32 - the engine's keys and cell offsets are 64-bit.  n = 2^23 vertices x 3 walks x length 255 is 6.4 G
+    corpus cells (25.7 GB): everything above walk 16.8 M lives beyond 2^32.  The graph is small (an RMAT scale-12 block on
+    the LOWEST ids, a copy on the HIGHEST ids - the walks whose keys exceed 2^32 - and edges across), the rest of the
+    vertices are isolated, so the 64-bit C oracle (oracle/wharf_oracle.c) finishes in seconds.  Compared: step counts,
+    corpus fingerprints, affected ids and positions after a batch on the high block, and walks read back from both ends."""
+    import psutil
+    from oracle import wharf_oracle as wo
+    if psutil.virtual_memory().available < (80 << 30):
+        pytest.skip("needs 80 GB of host memory for the oracle's corpus")
+    scale, block = 23, 1 << 12
+    n = 1 << scale
+    off12, adj12 = wo.rmat_graph(12, 16000, 5)
+    low = np.stack([np.repeat(np.arange(block, dtype=np.int64), np.diff(np.append(off12, adj12.shape[0]).astype(np.int64))), adj12.astype(np.int64)], 1)
+    high = low + (n - block)
+    rng = np.random.default_rng(11)
+    cross = np.stack([rng.integers(0, block, 3000), rng.integers(n - block, n, 3000)], 1)
+    pairs = np.concatenate([low, high, cross, cross[:, ::-1]])
+    pairs = np.unique(pairs[pairs[:, 0] != pairs[:, 1]], axis=0)                       # sorted by (src, dst), unique
+    off, adj = wo.csr_from_sorted_pairs(n, pairs.astype(np.uint32))
+    wpv, length = 3, 255
+    assert n * wpv * length > (1 << 32)
+    batch = np.stack([rng.integers(n - block, n, 400), rng.integers(n - block, n, 400)], 1).astype(np.uint32)
+    batch = np.concatenate([batch, batch[:, ::-1]])
+    for det in (True, False):
+        model_o, model_e = (wo.DEEPWALK, wharf.DEEPWALK) if det else (wo.NODE2VEC, wharf.NODE2VEC)
+        o = wo.Oracle(n, off, adj, walks_per_vertex=wpv, walk_length=length, model=model_o, p=0.5, q=2.0, deterministic=det, seed=3)
+        cfg = wharf.Config(walks_per_vertex=wpv, walk_length=length, random_walk_model=model_e, paramP=0.5, paramQ=2.0,
+                           deterministic_mode=det, seed=3, search_mode=wharf.SEARCH_SCAN)
+        with wharf.WharfMH(n, int(adj.shape[0]), off, adj, config=cfg) as e:
+            assert e.generate_initial_random_walks() == o.generate()
+            ow = o.walks()
+            assert e.corpus_fingerprint() == wo.corpus_fingerprint(ow)
+            probe = [0, 5, n - 1, n, 2 * n + n - 7, 3 * n - 1, 2 * n + n - block + 17]   # the last ones: keys beyond 2^32
+            assert max(probe) * length > (1 << 32)
+            assert np.array_equal(e.walks_gather(probe), ow[probe])
+            assert e.walk(3 * n - 1) == "".join(f"{v} " for v in ow[3 * n - 1][ow[3 * n - 1] != wo.NO_VERTEX])
+            o.update(batch.copy(), delete=False, remove_dups=True)
+            affected = e.insert_edges_batch(batch.copy(), remove_dups=True)
+            ids, pos = o.affected()
+            assert ids.max() * length > (1 << 32) and np.array_equal(affected, ids)
+            assert np.array_equal(e.affected_walks()[1], pos)
+            assert e.corpus_fingerprint() == wo.corpus_fingerprint(o.walks())
+            assert np.array_equal(e.walks_gather(probe), o.walks()[probe])
+        del o, ow

@@ -650,3 +650,99 @@ def test_generate_to_host_equals_generate_then_copy(wharf, wo, mode):
         pageable = np.zeros_like(expect)
         assert b.generate_initial_random_walks_to_host(pageable) == steps
         assert np.array_equal(pageable, expect)
+
+
+def _sym_pairs(pairs):
+    pairs = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
+    both = np.concatenate([pairs, pairs[:, ::-1]])
+    both = both[both[:, 0] != both[:, 1]]
+    return np.unique(both, axis=0).astype(np.uint32)
+
+
+@pytest.mark.parametrize("init", ["weight", "burnin"])
+def test_triangle_filter_symmetric_batches_vs_oracle(wharf, wo, init, monkeypatch):
+    """node2vec's membership test answered from the aux word of the proposal's own slot (triangle blocks, wmh_neighbour_filter
+    == 2) on a triangle-rich symmetric graph: inserts that close triangles between edges of the same batch, a batch that
+    deletes triangle edges (bits stay behind: a superset), enough deletes to force a rebuild, then a DIRECTED batch, which
+    must drop the engine back to per-row blocks.  The corpus equals the keyed oracle after every step, and equals the
+    corpus of an engine that never used triangle blocks (WHARF_TRI=0)."""
+    rng = np.random.default_rng(17)
+    n = 1 << 8
+    off, adj = wo.rmat_graph(8, 3000, seed=9)                         # ~20 neighbours per vertex on 256 vertices: many triangles
+    ini = {"weight": wo.INIT_WEIGHT, "burnin": wo.INIT_BURNIN}[init]
+    kw = dict(walks_per_vertex=6, walk_length=30)
+    o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, init_strategy=ini, seed=5, **kw)
+    corpora = []
+    with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False,
+              sampler_init_strategy=ini, seed=5, **kw) as e:
+        assert e.neighbour_filter() == 0
+        assert e.generate_initial_random_walks() == o.generate()
+        assert e.neighbour_filter() == 2
+        assert np.array_equal(e.walks(), o.walks())
+        corpora.append(e.walks())
+        ops = []
+        for step in range(10):
+            row_ptr, col = o.csr()
+            if step % 3 == 2:                                         # delete existing edges, both directions: triangle edges among them
+                src = np.repeat(np.arange(n), np.diff(row_ptr).astype(np.int64))
+                pick = rng.choice(col.shape[0], 300 if step != 8 else col.shape[0] // 3, replace=False)
+                b, delete = _sym_pairs(np.stack([src[pick], col[pick]], 1)), True
+            else:                                                     # a clique on 6 random vertices + random edges: triangles inside one batch
+                clique = rng.choice(n, 6, replace=False)
+                extra = rng.integers(0, n, (60, 2))
+                b, delete = _sym_pairs(np.concatenate([[(u, v) for u in clique for v in clique if u < v], extra])), False
+            ops.append((b, delete))
+            o.update(b.copy(), delete=delete, remove_dups=True)
+            (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
+            assert e.neighbour_filter() == 2
+            assert np.array_equal(e.affected_walks()[0], o.affected()[0])
+            assert np.array_equal(e.walks(), o.walks()), f"step {step}"
+            corpora.append(e.walks())
+        e.destroy_index()                                             # a fresh corpus on the updated graph, blocks as maintained
+        assert e.generate_initial_random_walks() == o.generate() and np.array_equal(e.walks(), o.walks())
+        directed = rng.integers(0, n, (40, 2)).astype(np.uint32)      # no reverse edges: the blocks no longer hold
+        o.update(directed.copy(), delete=False, remove_dups=True)
+        e.insert_edges_batch(directed.copy(), remove_dups=True)
+        assert e.neighbour_filter() == 1
+        assert np.array_equal(e.walks(), o.walks())
+        b = _sym_pairs(rng.integers(0, n, (50, 2)))
+        o.update(b.copy(), delete=False, remove_dups=True)
+        e.insert_edges_batch(b.copy(), remove_dups=True)
+        assert e.neighbour_filter() == 1 and np.array_equal(e.walks(), o.walks())
+    monkeypatch.setenv("WHARF_TRI", "0")
+    with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False,
+              sampler_init_strategy=ini, seed=5, **kw) as e:
+        e.generate_initial_random_walks()
+        assert e.neighbour_filter() == 1 and np.array_equal(e.walks(), corpora[0])
+        for (b, delete), want in zip(ops, corpora[1:]):
+            (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
+            assert np.array_equal(e.walks(), want)
+
+
+@pytest.mark.parametrize("coop", ["0", "1"])
+def test_triangle_filter_hub_rows(wharf, wo, coop, monkeypatch):
+    """Slots whose BOTH rows are long (hub - hub edges) take the block-per-slot kernels, at build time and when an inserted
+    edge joins two hubs; a directed start graph never gets triangle blocks.  coop = 1: membership searches in rows of 1024
+    neighbours and more are done by the whole warp (32 probes per round, WHARF_COOP_SEARCH) - the same corpus."""
+    monkeypatch.setenv("WHARF_COOP_SEARCH", coop)
+    rng = np.random.default_rng(23)
+    n, leaves = 6000, 5000
+    edges = [(h, v) for h in (0, 1, 2) for v in range(3, leaves)] + [(0, 1)] + rng.integers(3, n, (4000, 2)).tolist()
+    pairs = _sym_pairs(edges)
+    off, adj = wo.csr_from_sorted_pairs(n, pairs)
+    kw = dict(walks_per_vertex=2, walk_length=12)
+    o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, seed=8, **kw)
+    with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False, seed=8, **kw) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        assert e.neighbour_filter() == 2 and e.degree(0) > 2048 and e.degree(2) > 2048
+        assert np.array_equal(e.walks(), o.walks())
+        for b, delete in ((_sym_pairs([(0, 2), (1, 2), (5, 6)]), False), (_sym_pairs([(0, 1), (7, 8)]), True), (_sym_pairs([(0, 1)]), False)):
+            o.update(b.copy(), delete=delete, remove_dups=True)
+            (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
+            assert e.neighbour_filter() == 2 and np.array_equal(e.walks(), o.walks())
+    directed = pairs[pairs[:, 0] < pairs[:, 1]]                       # one direction only
+    doff, dadj = wo.csr_from_sorted_pairs(n, directed)
+    o = wo.Oracle(n, doff, dadj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, seed=8, **kw)
+    with make(wharf, n, doff, dadj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False, seed=8, **kw) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        assert e.neighbour_filter() == 1 and np.array_equal(e.walks(), o.walks())

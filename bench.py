@@ -455,6 +455,7 @@ def run_updates(ctx, engine, n, sizes, insert_only, search_name):
     if ctx.world > 1:
         from dynamicgraphrepresentationlearning_b200.distributed import ShardedWharfMH
         sharded = ShardedWharfMH.from_engine(engine)
+        sharded.warm_collectives()                                   # NCCL channel set-up is not batch latency
     names = {wharf.SEARCH_INDEX: "index", wharf.SEARCH_SCAN: "scan", 0: "none"}
     rows = []
     for b, size in enumerate(sizes):

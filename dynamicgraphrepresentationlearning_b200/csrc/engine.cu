@@ -283,6 +283,32 @@ void finish_graph(wmh_engine& e, u64 n, u64 m, const u64* d_offsets, const u32* 
     e.bitmap.allocate((n + 31) / 32);
     WHARF_CUDA(cudaStreamSynchronize(e.stream));
     tr.mark("create: graph buffers+copy");
+    // Tuning aid only: WHARF_L2_PERSIST=<MiB> asks the L2 to keep that much of the row descriptors resident (access-policy
+    // window on the engine's stream) while the neighbour pool streams past them.  Changes process-wide device state
+    // (cudaLimitPersistingL2CacheSize), hence off unless asked for; measured in profiles/r02c_l2_persist_ab.txt.
+    if (const char* env = std::getenv("WHARF_L2_PERSIST"))
+    {
+        const size_t want = (size_t) std::atoi(env) << 20;
+        int max_persist = 0, max_window = 0;
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, e.cfg.device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, e.cfg.device);
+        const size_t carve = std::min(want, (size_t) max_persist);
+        if (carve)
+        {
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve);
+            cudaStreamAttrValue attr{};
+            attr.accessPolicyWindow.base_ptr = e.g.desc.ptr;
+            attr.accessPolicyWindow.num_bytes = std::min(n * sizeof(RowDesc), (size_t) max_window);
+            attr.accessPolicyWindow.hitRatio = (float) std::min(1.0, (double) carve / (double) attr.accessPolicyWindow.num_bytes);
+            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            cudaStreamSetAttribute(e.stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+            if (std::getenv("WHARF_TRACE"))
+                std::fprintf(stderr, "[wharf] L2 persist: carve %zu MiB (max %d MiB), window %zu MiB, hit ratio %.2f: %s\n", carve >> 20, max_persist >> 20,
+                             attr.accessPolicyWindow.num_bytes >> 20, attr.accessPolicyWindow.hitRatio, cudaGetErrorString(cudaGetLastError()));
+            cudaGetLastError();
+        }
+    }
 }
 
 // The partition of the walks the engine would use for a corpus generated now.

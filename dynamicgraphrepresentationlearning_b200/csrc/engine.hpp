@@ -153,7 +153,6 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int 
 // Aux tails (MH node2vec): switch the layout on (one compaction), rebuild every tail (filter set, caches empty), or
 // only empty the sampler caches.
 void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g);
-bool graph_is_symmetric(const LaunchCtx& lc, const DeviceGraph& g);   // every edge v -> c has its twin c -> v
 void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g);
 void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g);
 void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr /* n+1 */, u32* d_col /* m */);

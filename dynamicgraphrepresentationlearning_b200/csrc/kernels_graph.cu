@@ -288,19 +288,22 @@ __global__ void __launch_bounds__(256) aux_invalidate_kernel(const RowDesc* __re
 constexpr u32 kTriChunk = 128;       // slots of one row handled by one warp (four 8-lane groups x 32 slots)
 constexpr u32 kTriHeavy = 2048;      // slots whose smaller row is longer than this go to a block of their own
 
-// N(v) n N(c) as a Bloom block, by the lanes `sub` of `lanes` cooperating lanes: every member of the shorter row is
-// searched in the longer one.  The caller ORs the partial results.
-__device__ __forceinline__ u32 tri_block_partial(const u32* __restrict__ pool, uint2 dv, uint2 dc, u32 sub, u32 lanes)
+// Scratch of a build: one 16-bit block per edge slot, row v owning blocks[eoff[v], eoff[v] + degree) - the per-row
+// neighbour filter of common.cuh (element x sets filter_bits(h(x)) in block filter_block(h(x), degree)).  A membership
+// question is answered by ONE 2-byte load in most cases (a clear bit proves absence); the binary search runs for the rest.
+struct TriFilter
 {
-    const uint2 small = dv.y <= dc.y ? dv : dc, large = dv.y <= dc.y ? dc : dv;
-    u32 bits = 0;
-    for (u32 k = sub; k < small.y; k += lanes)
-    {
-        const u32 x = __ldg(pool + small.x + 2 * (u64) k);
-        const u32 r = lower_bound_row(pool + large.x, large.y, x, 1);
-        if (r < large.y && __ldg(pool + large.x + 2 * (u64) r) == x) bits |= filter_bits(filter_hash(x));
-    }
-    return bits;
+    const unsigned short* blocks;
+    const u32* eoff;
+};
+
+__device__ __forceinline__ bool tri_member(const u32* __restrict__ pool, uint2 row, u32 row_off, u32 x, const TriFilter& f)
+{
+    const u32 h = filter_hash(x);
+    const u32 need = filter_bits(h);
+    if ((f.blocks[row_off + filter_block(h, row.y)] & need) != need) return false;
+    const u32 r = lower_bound_row(pool + row.x, row.y, x, 1);
+    return r < row.y && __ldg(pool + row.x + 2 * (u64) r) == x;
 }
 
 __device__ __forceinline__ void tri_store(u32* __restrict__ pool, uint2 dv, u32 i, u32 bits)
@@ -311,91 +314,148 @@ __device__ __forceinline__ void tri_store(u32* __restrict__ pool, uint2 dv, u32 
 struct TriChunksOf
 {
     const RowDesc* desc;
-    const u32* rows;      // nullptr: every vertex
     u64 count;
-    __device__ u64 operator()(u64 j) const
-    {
-        if (j >= count) return 0;
-        const u32 v = rows ? rows[j] : (u32) j;
-        return (desc[v].degree + kTriChunk - 1) / kTriChunk;
-    }
+    __device__ u64 operator()(u64 v) const { return v < count ? (desc[v].degree + kTriChunk - 1) / kTriChunk : 0; }
 };
 
-// One warp per chunk of kTriChunk slots of a row (rows == nullptr: all rows; else the listed rows).  mirror: also store the
-// block into the slot c -> v (the same set on a symmetric graph) - used when only some rows are rebuilt.
-__global__ void __launch_bounds__(256) tri_build_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ rows,
-                                                        u64 n_rows, const u64* __restrict__ chunk_scan, u64 n_chunks, bool mirror,
-                                                        uint2* __restrict__ heavy, u32* __restrict__ heavy_count, u32 heavy_capacity)
+struct DegreeOfRow
+{
+    const RowDesc* desc;
+    u64 count;
+    __device__ u32 operator()(u32 v) const { return v < count ? desc[v].degree : 0u; }
+};
+
+// One warp per chunk of kTriChunk elements of a row: the row's per-row filter blocks into the scratch array (zeroed before).
+__global__ void __launch_bounds__(256) tri_rowfilter_kernel(const RowDesc* __restrict__ desc, const u32* __restrict__ pool, u64 n,
+                                                            const u64* __restrict__ chunk_scan, u64 n_chunks, const u32* __restrict__ eoff,
+                                                            u32* __restrict__ blocks_as_words)
+{
+    const u64 chunk = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (chunk >= n_chunks) return;
+    const u32 lane = threadIdx.x & 31;
+    const u32 v = upper_segment_u64(chunk_scan, (u32) n + 1, chunk);
+    const uint2 dv = reinterpret_cast<const uint2*>(desc)[v];
+    const u32 first = (u32) (chunk - chunk_scan[v]) * kTriChunk, last = min(dv.y, first + kTriChunk);
+    const u32 off = eoff[v];
+    for (u32 i = first + lane; i < last; i += 32)
+    {
+        const u32 h = filter_hash(__ldg(pool + dv.x + 2 * (u64) i));
+        const u32 slot = off + filter_block(h, dv.y);                         // 16-bit block `slot`: half of word slot / 2
+        atomicOr(blocks_as_words + (slot >> 1), filter_bits(h) << ((slot & 1) * 16));
+    }
+}
+
+// One warp per chunk of kTriChunk slots of a row u, an 8-lane group per slot u -> w.  A pair {u, w} is handled ONCE, from the
+// row of its longer member (ties: the larger id): the lanes scan N(w) - short and contiguous - and look every element up in
+// the filter and the row of u, which all slots of the chunk share (L1 / L2-hot; looking the members of the short row up
+// from the short row's side sent one random DRAM fetch per lookup: 8.6 ms at scale-20).  The block goes to slot u -> w and
+// to its twin w -> u, whose position falls out of the scan.  counters[1] |= 1 when a twin is missing, counters[2] counts the
+// slots written: a graph is symmetric exactly when no twin is missing and every slot was written.
+__global__ void __launch_bounds__(256) tri_build_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, u64 n,
+                                                        const u64* __restrict__ chunk_scan, u64 n_chunks, TriFilter f,
+                                                        uint2* __restrict__ heavy, u32 heavy_capacity, u32* __restrict__ counters)
 {
     const u64 chunk = ((u64) blockIdx.x * 256 + threadIdx.x) >> 5;
     if (chunk >= n_chunks) return;
     const u32 lane = threadIdx.x & 31, sub = lane & 7, group = lane >> 3;
-    const u32 j = upper_segment_u64(chunk_scan, (u32) n_rows + 1, chunk);
-    const u32 v = rows ? rows[j] : j;
-    const uint2 dv = reinterpret_cast<const uint2*>(desc)[v];
-    const u32 first = (u32) (chunk - chunk_scan[j]) * kTriChunk;
-    const u32 last = min(dv.y, first + kTriChunk);
+    const u32 u = upper_segment_u64(chunk_scan, (u32) n + 1, chunk);
+    const uint2 du = reinterpret_cast<const uint2*>(desc)[u];
+    const u32 off_u = f.eoff[u];
+    const u32 first = (u32) (chunk - chunk_scan[u]) * kTriChunk;
+    const u32 last = min(du.y, first + kTriChunk);
+    u32 written = 0;
     for (u32 i0 = first; i0 < last; i0 += 4)                      // uniform trip count: the shuffles below need the whole warp
     {
         const u32 i = i0 + group;
         const bool has = i < last;
-        u32 c = 0;
-        uint2 dc = make_uint2(0, 0);
+        u32 w = 0;
+        uint2 dw = make_uint2(0, 0);
         if (has)
         {
-            c = __ldg(pool + dv.x + 2 * (u64) i);
-            dc = reinterpret_cast<const uint2*>(desc)[c];
+            w = __ldg(pool + du.x + 2 * (u64) i);
+            dw = reinterpret_cast<const uint2*>(desc)[w];
         }
-        const bool is_heavy = has && min(dv.y, dc.y) > kTriHeavy;
-        u32 bits = (has && !is_heavy) ? tri_block_partial(pool, dv, dc, sub, 8) : 0u;
-        bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
-        bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
-        bits |= __shfl_xor_sync(0xffffffffu, bits, 4);
-        if (has && sub == 0)
+        const bool mine = has && (dw.y < du.y || (dw.y == du.y && w <= u));
+        const bool is_heavy = mine && dw.y > kTriHeavy;
+        u32 bits = 0, twin = 0xFFFFFFFFu;
+        if (mine && !is_heavy)
+            for (u32 k = sub; k < dw.y; k += 8)
+            {
+                const u32 x = __ldg(pool + dw.x + 2 * (u64) k);
+                if (x == u) twin = k;
+                if (tri_member(pool, du, off_u, x, f)) bits |= filter_bits(filter_hash(x));
+            }
+#pragma unroll
+        for (u32 d = 1; d < 8; d <<= 1)
+        {
+            bits |= __shfl_xor_sync(0xffffffffu, bits, d);
+            twin = min(twin, __shfl_xor_sync(0xffffffffu, twin, d));
+        }
+        if (mine && sub == 0)
         {
             if (is_heavy)
             {
-                const u32 at = atomicAdd(heavy_count, 1u);
-                if (at < heavy_capacity) heavy[at] = make_uint2(v, i);
-                else tri_store(pool, dv, i, 0xFFFFu);              // list full: "maybe" for every query, the exact search decides
+                const u32 at = atomicAdd(counters, 1u);
+                if (at < heavy_capacity) heavy[at] = make_uint2(u, i);
+                else                                                  // list full: "maybe" for every query, the exact search decides
+                {
+                    const u32 r = lower_bound_row(pool + dw.x, dw.y, u, 1);
+                    if (r < dw.y && __ldg(pool + dw.x + 2 * (u64) r) == u)
+                    {
+                        tri_store(pool, du, i, 0xFFFFu);
+                        if (w != u) tri_store(pool, dw, r, 0xFFFFu);
+                        written += (w != u) ? 2 : 1;
+                    }
+                    else counters[1] = 1u;
+                }
             }
+            else if (twin == 0xFFFFFFFFu) counters[1] = 1u;
             else
             {
-                tri_store(pool, dv, i, bits);
-                if (mirror)
-                {
-                    const u32 r = lower_bound_row(pool + dc.x, dc.y, v, 1);
-                    if (r < dc.y && pool[dc.x + 2 * (u64) r] == v) tri_store(pool, dc, r, bits);
-                }
+                tri_store(pool, du, i, bits);
+                if (w != u) tri_store(pool, dw, twin, bits);
+                written += (w != u) ? 2 : 1;
             }
         }
     }
+#pragma unroll
+    for (u32 d = 16; d; d >>= 1) written += __shfl_xor_sync(0xffffffffu, written, d);
+    if (lane == 0 && written) atomicAdd(counters + 2, written);
 }
 
-// One block per heavy slot (both rows long: hub - hub edges).
-__global__ void __launch_bounds__(256) tri_heavy_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const uint2* __restrict__ heavy,
-                                                        const u32* __restrict__ heavy_count, u32 heavy_capacity, bool mirror)
+// One block per heavy pair (both rows long: hub - hub edges).
+__global__ void __launch_bounds__(256) tri_heavy_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, TriFilter f,
+                                                        const uint2* __restrict__ heavy, u32 heavy_capacity, u32* __restrict__ counters)
 {
-    __shared__ u32 s_bits;
-    const u32 count = min(*heavy_count, heavy_capacity);
+    __shared__ u32 s_bits, s_twin;
+    const u32 count = min(counters[0], heavy_capacity);
     for (u32 h = blockIdx.x; h < count; h += gridDim.x)
     {
         const uint2 item = heavy[h];
-        const uint2 dv = reinterpret_cast<const uint2*>(desc)[item.x];
-        const u32 c = pool[dv.x + 2 * (u64) item.y];
-        const uint2 dc = reinterpret_cast<const uint2*>(desc)[c];
-        if (threadIdx.x == 0) s_bits = 0;
+        const u32 u = item.x;
+        const uint2 du = reinterpret_cast<const uint2*>(desc)[u];
+        const u32 off_u = f.eoff[u];
+        const u32 w = pool[du.x + 2 * (u64) item.y];
+        const uint2 dw = reinterpret_cast<const uint2*>(desc)[w];
+        if (threadIdx.x == 0) { s_bits = 0; s_twin = 0xFFFFFFFFu; }
         __syncthreads();
-        const u32 bits = tri_block_partial(pool, dv, dc, threadIdx.x, 256);
+        u32 bits = 0;
+        for (u32 k = threadIdx.x; k < dw.y; k += 256)
+        {
+            const u32 x = __ldg(pool + dw.x + 2 * (u64) k);
+            if (x == u) s_twin = k;
+            if (tri_member(pool, du, off_u, x, f)) bits |= filter_bits(filter_hash(x));
+        }
         if (bits) atomicOr(&s_bits, bits);
         __syncthreads();
         if (threadIdx.x == 0)
         {
-            tri_store(pool, dv, item.y, s_bits);
-            if (mirror)
+            if (s_twin == 0xFFFFFFFFu) counters[1] = 1u;
+            else
             {
-                const u32 r = lower_bound_row(pool + dc.x, dc.y, item.x, 1);
-                if (r < dc.y && pool[dc.x + 2 * (u64) r] == item.x) tri_store(pool, dc, r, s_bits);
+                tri_store(pool, du, item.y, s_bits);
+                if (w != u) tri_store(pool, dw, s_twin, s_bits);
+                atomicAdd(counters + 2, (w != u) ? 2u : 1u);
             }
         }
         __syncthreads();
@@ -490,22 +550,6 @@ __global__ void __launch_bounds__(256) tri_insert_heavy_kernel(const RowDesc* __
         __syncthreads();
         if (threadIdx.x == 0 && s_bits) atomicOr(pool + da.x + 2 * (u64) rb + 1, s_bits << 16);
         __syncthreads();
-    }
-}
-
-// flag |= 1 when some edge v -> c has no twin c -> v (one thread per slot of a chunked row walk is overkill: 8 lanes per row).
-__global__ void __launch_bounds__(256) symmetric_graph_kernel(const RowDesc* __restrict__ desc, u64 n, const u32* __restrict__ pool, u32 rs, u32* __restrict__ flag)
-{
-    const u64 g = ((u64) blockIdx.x * 256 + threadIdx.x) >> 3;
-    const u32 sub = threadIdx.x & 7;
-    if (g >= n) return;
-    const uint2 dv = reinterpret_cast<const uint2*>(desc)[g];
-    for (u32 i = sub; i < dv.y; i += 8)
-    {
-        const u32 c = pool[dv.x + ((u64) i << rs)];
-        const uint2 dc = reinterpret_cast<const uint2*>(desc)[c];
-        const u32 r = lower_bound_row(pool + dc.x, dc.y, (u32) g, rs);
-        if (r >= dc.y || pool[dc.x + ((u64) r << rs)] != (u32) g) { *flag = 1; return; }
     }
 }
 
@@ -819,7 +863,7 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int 
         // rows just moved into the interleaved layout (aux words zero): triangle blocks while the graph is symmetric
         // (WHARF_TRI=0 keeps per-row blocks: A/B measurements), per-row blocks otherwise
         const char* env = std::getenv("WHARF_TRI");
-        g.tri = (!(env && std::atoi(env) == 0) && graph_is_symmetric(lc, g)) ? 1u : 0u;
+        g.tri = (env && std::atoi(env) == 0) ? 0u : 1u;             // the build itself checks the symmetry and falls back
         g.tri_stale = 0;
         graph_aux_rebuild(lc, g);
     }
@@ -828,51 +872,54 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int 
     tr.mark("compact: repoint+aux");
 }
 
-bool graph_is_symmetric(const LaunchCtx& lc, const DeviceGraph& g)
-{
-    if (g.n == 0) return true;
-    Scratch<u32> flag(lc.stream, 1);
-    WHARF_CUDA(cudaMemsetAsync(flag.ptr, 0, 4, lc.stream));
-    symmetric_graph_kernel<<<div_up(g.n * 8, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr, g.tail, flag.ptr);
-    lc.count();
-    WHARF_CUDA(cudaGetLastError());
-    u32 bad = 0;
-    WHARF_CUDA(cudaMemcpyAsync(&bad, flag.ptr, 4, cudaMemcpyDeviceToHost, lc.stream));
-    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
-    return bad == 0;
-}
-
 namespace
 {
 constexpr u32 kTriHeavyCapacity = 1u << 22;      // hub - hub slots parked for the block-per-slot kernel (32 MB of scratch)
 
-// Triangle blocks of every slot of the listed rows (rows == nullptr: all rows).  mirror: the twin slots c -> v get the same
-// block (partial rebuilds).
-void tri_build(const LaunchCtx& lc, DeviceGraph& g, const u32* d_rows, u64 n_rows, bool mirror)
+// Triangle blocks of every slot.  Returns false when the graph is not symmetric (some edge has no twin): the blocks are then
+// meaningless and the caller falls back to per-row blocks.
+bool tri_build_all(const LaunchCtx& lc, DeviceGraph& g)
 {
-    if (n_rows == 0) return;
-    Scratch<u64> chunk_scan(lc.stream, n_rows + 1);
+    const u64 n = g.n;
+    if (n == 0 || g.m == 0) return true;
+    Scratch<u64> chunk_scan(lc.stream, n + 1);
+    Scratch<u32> eoff(lc.stream, n + 1);
     {
         cub::CountingInputIterator<u64> iota(0);
-        cub::TransformInputIterator<u64, TriChunksOf, cub::CountingInputIterator<u64>> chunks(iota, TriChunksOf{g.desc.ptr, d_rows, n_rows});
-        size_t temp_bytes = 0;
-        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, chunks, chunk_scan.ptr, (i64) (n_rows + 1), lc.stream));
-        Scratch<u8> temp(lc.stream, temp_bytes);
-        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(temp.ptr, temp_bytes, chunks, chunk_scan.ptr, (i64) (n_rows + 1), lc.stream));
-        lc.count_lib();
+        cub::TransformInputIterator<u64, TriChunksOf, cub::CountingInputIterator<u64>> chunks(iota, TriChunksOf{g.desc.ptr, n});
+        cub::CountingInputIterator<u32> iota32(0);
+        cub::TransformInputIterator<u32, DegreeOfRow, cub::CountingInputIterator<u32>> degrees(iota32, DegreeOfRow{g.desc.ptr, n});
+        size_t bytes_a = 0, bytes_b = 0;
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, bytes_a, chunks, chunk_scan.ptr, (i64) (n + 1), lc.stream));
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, bytes_b, degrees, eoff.ptr, (i64) (n + 1), lc.stream));
+        Scratch<u8> temp(lc.stream, std::max(bytes_a, bytes_b));
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(temp.ptr, bytes_a, chunks, chunk_scan.ptr, (i64) (n + 1), lc.stream));
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(temp.ptr, bytes_b, degrees, eoff.ptr, (i64) (n + 1), lc.stream));
+        lc.count_lib(2);
     }
     u64 n_chunks = 0;
-    WHARF_CUDA(cudaMemcpyAsync(&n_chunks, chunk_scan.ptr + n_rows, 8, cudaMemcpyDeviceToHost, lc.stream));
+    u32 slots = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&n_chunks, chunk_scan.ptr + n, 8, cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaMemcpyAsync(&slots, eoff.ptr + n, 4, cudaMemcpyDeviceToHost, lc.stream));
     WHARF_CUDA(cudaStreamSynchronize(lc.stream));
-    if (n_chunks == 0) return;
+    if (n_chunks == 0) return true;
+    const u64 words = (u64) slots / 2 + 2;
+    Scratch<u32> blocks(lc.stream, words);                           // one 16-bit per-row filter block per slot
     Scratch<uint2> heavy(lc.stream, kTriHeavyCapacity);
-    Scratch<u32> heavy_count(lc.stream, 1);
-    WHARF_CUDA(cudaMemsetAsync(heavy_count.ptr, 0, 4, lc.stream));
-    tri_build_kernel<<<div_up(n_chunks * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, d_rows, n_rows, chunk_scan.ptr, n_chunks, mirror,
-                                                                        heavy.ptr, heavy_count.ptr, kTriHeavyCapacity);
-    tri_heavy_kernel<<<lc.sm_count * 4, 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, heavy.ptr, heavy_count.ptr, kTriHeavyCapacity, mirror);
-    lc.count(2);
+    Scratch<u32> counters(lc.stream, 4);                             // [0] heavy pairs, [1] a twin is missing, [2] slots written
+    WHARF_CUDA(cudaMemsetAsync(blocks.ptr, 0, words * sizeof(u32), lc.stream));
+    WHARF_CUDA(cudaMemsetAsync(counters.ptr, 0, 16, lc.stream));
+    const unsigned grid = div_up(n_chunks * 32, 256);
+    tri_rowfilter_kernel<<<grid, 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, n, chunk_scan.ptr, n_chunks, eoff.ptr, blocks.ptr);
+    const TriFilter f{reinterpret_cast<const unsigned short*>(blocks.ptr), eoff.ptr};
+    tri_build_kernel<<<grid, 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, n, chunk_scan.ptr, n_chunks, f, heavy.ptr, kTriHeavyCapacity, counters.ptr);
+    tri_heavy_kernel<<<lc.sm_count * 4, 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, f, heavy.ptr, kTriHeavyCapacity, counters.ptr);
+    lc.count(3);
     WHARF_CUDA(cudaGetLastError());
+    u32 host[4] = {0, 0, 0, 0};
+    WHARF_CUDA(cudaMemcpyAsync(host, counters.ptr, 16, cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
+    return host[1] == 0 && host[2] == slots;
 }
 }  // namespace
 
@@ -882,9 +929,9 @@ void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g)
     if (g.tri)
     {
         graph_aux_clear_caches(lc, g);                            // cache halves empty; the build overwrites every filter half
-        tri_build(lc, g, nullptr, g.n, false);
         g.tri_stale = 0;
-        return;
+        if (tri_build_all(lc, g)) return;
+        g.tri = 0;                                                // some edge has no twin: per-row blocks
     }
     aux_build_all_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr);
     lc.count();

@@ -117,6 +117,20 @@ class ShardedWharfMH:
         parts = [gathered[r * width: r * width + int(counts[r].item())] for r in range(self.world)]
         return np.sort(torch.cat(parts).cpu().numpy().astype(np.uint64))
 
+    def warm_collectives(self) -> None:
+        """One untimed round of the collectives an update uses (broadcast, all-gather, device sort): NCCL opens its channels
+        for each collective kind on first use (71 ms for the first all-gather at N = 2), which is set-up, not batch latency."""
+        count = torch.zeros(1, dtype=torch.int64, device=self.device)
+        dist.broadcast(count, src=0, group=self.group)
+        pairs = torch.zeros((16, 2), dtype=torch.int32, device=self.device)
+        dist.broadcast(pairs, src=0, group=self.group)
+        ids = torch.arange(4, dtype=torch.int64, device=self.device) + 4 * self.rank
+        if self._on_gpu:
+            self.all_gather_ids_device(ids)
+            torch.cuda.synchronize(self.device)
+        else:
+            self.all_gather_ids(ids.numpy().astype(np.uint64))
+
     # -- dygrl::WharfMH surface -----------------------------------------------------------------------
     def number_of_vertices(self) -> int:
         return self.engine.number_of_vertices()

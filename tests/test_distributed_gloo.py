@@ -88,6 +88,7 @@ def _worker(rank, world, port, out_dir):
         sharded = ShardedWharfMH(n, adj.shape[0], off, adj, config=cfg, engine_factory=lambda c: OracleShard(wo, n, off, adj, c))
         single = wo.Oracle(n, off, adj, walks_per_vertex=3, walk_length=9)
         assert sharded.generate_initial_random_walks() == single.generate()
+        sharded.warm_collectives()                                # an untimed round of the update's collectives: no state change
         ok = True
         for seed, delete in ((0, False), (1, False), (0, True)):
             batch = wo.generate_batch(20, n, seed, False, False)

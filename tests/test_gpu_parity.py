@@ -746,3 +746,31 @@ def test_triangle_filter_hub_rows(wharf, wo, coop, monkeypatch):
     with make(wharf, n, doff, dadj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False, seed=8, **kw) as e:
         assert e.generate_initial_random_walks() == o.generate()
         assert e.neighbour_filter() == 1 and np.array_equal(e.walks(), o.walks())
+
+
+def test_triangle_filter_symmetry_detection(wharf, wo):
+    """The triangle build decides by itself whether the graph is symmetric: a pair is handled once, from its longer row, and
+    the count of slots written must reach the edge count.  One missing twin - seen from the longer row or from the shorter
+    one - sends the engine to per-row blocks; self-loops are their own twins and keep triangle blocks.  Exact either way."""
+    rng = np.random.default_rng(31)
+    n = 300
+    base = _sym_pairs(np.concatenate([[(0, v) for v in range(1, 120)], rng.integers(0, n, (900, 2))]))
+    loops = np.array([(5, 5), (0, 0), (77, 77)], dtype=np.uint32)
+    kw = dict(walks_per_vertex=3, walk_length=20)
+    cases = {"loops": (np.concatenate([base, loops]), 2)}
+    assert ((base[:, 0] == 0) & (base[:, 1] == 50)).sum() == 1
+    cases["hub side missing"] = (base[~((base[:, 0] == 0) & (base[:, 1] == 50))], 1)      # 50 -> 0 without 0 -> 50
+    cases["leaf side missing"] = (base[~((base[:, 0] == 50) & (base[:, 1] == 0))], 1)     # 0 -> 50 without 50 -> 0
+    for name, (pairs, want) in cases.items():
+        pairs = np.unique(pairs.astype(np.int64), axis=0).astype(np.uint32)
+        off, adj = wo.csr_from_sorted_pairs(n, pairs)
+        o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, seed=3, **kw)
+        with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False, seed=3, **kw) as e:
+            assert e.generate_initial_random_walks() == o.generate(), name
+            assert e.neighbour_filter() == want, name
+            assert np.array_equal(e.walks(), o.walks()), name
+            b = _sym_pairs(rng.integers(0, n, (30, 2)))
+            o.update(b.copy(), delete=False, remove_dups=True)
+            e.insert_edges_batch(b.copy(), remove_dups=True)
+            assert e.neighbour_filter() == want and np.array_equal(e.walks(), o.walks()), name
+        o.close()

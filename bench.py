@@ -588,7 +588,12 @@ def run_workload(ctx, name, *, steps, warmup, e2e_iters, updates, headline):
     # ---- the reference-equivalent call: walks AND the inverted index built inside it (graph/wharfmh.h:312-354) ----
     cells = engine.number_of_local_walks() * LEN
     idx_steps = max(1, min(steps, 5))
-    if cells < (1 << 32) and cells * 16 < 0.5 * (torch.cuda.mem_get_info(ctx.dev)[0]):
+    chunk_cells = min(cells, 1 << 31)                        # the index sorts the corpus in chunks of whole positions (32-bit cell ids)
+    index_need = 4 * cells + 16 * chunk_cells + 8 * (n + 1) * -(-cells // max(chunk_cells, 1))
+    fits = index_need < 0.7 * torch.cuda.mem_get_info(ctx.dev)[0]
+    if ctx.world > 1:
+        fits = ctx.sum_over_ranks(0 if fits else 1) == 0
+    if fits:
         engine.set_config(search_mode=wharf.SEARCH_INDEX)
         run_i = timed_passes(ctx, engine, idx_steps, 1, peers)
         with_index_s = ctx.max_over_ranks((sum(run_i["kernel_ms"]) + sum(run_i["index_ms"])) * 1e-3)
@@ -602,8 +607,8 @@ def run_workload(ctx, name, *, steps, warmup, e2e_iters, updates, headline):
         engine.set_config(search_mode=wharf.SEARCH_SCAN)
     else:
         block["value_with_index"] = None
-        block["index_note"] = (f"no inverted index at this size on {world} GPU(s): {cells / 1e9:.1f} G cells per rank (32-bit cell ids hold 4.29 G; "
-                               "cells + sort buffers would not fit beside the 107 GB corpus on one GPU).  The corpus is the walk matrix and "
+        block["index_note"] = (f"no inverted index at this size on {world} GPU(s): {cells / 1e9:.1f} G cells per rank need {index_need / 1e9:.0f} GB "
+                               "(4 B per cell + the sort buffers of one 2^31-cell chunk) beside the corpus.  The corpus is the walk matrix and "
                                "affected walks are found by scanning it (search_mode SCAN), which needs no index")
 
     # ---- deterministic schedules side by side on the headline: the one-walker-per-thread kernel under the 68 B convention ----

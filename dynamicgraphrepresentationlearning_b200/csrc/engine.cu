@@ -591,14 +591,14 @@ void update(wmh_engine& e, u64 count, const u32* d_pairs, u32* d_sorted_out, boo
         }
         else if (e.cfg.search_mode == WMH_SEARCH_AUTO && e.index.valid)
         {
-            const u64 visited = index_count_touched(lc, e.index, batch.sources.ptr, batch.n_sources);
+            const u64 visited = index_count_touched(lc, e.index, e.g.n, batch.sources.ptr, batch.n_sources);
             use_index = visited * 8 < e.w_local * e.walks_L;    // a random index entry costs about 8 streamed cells
         }
         e.last_search = use_index ? WMH_SEARCH_INDEX : WMH_SEARCH_SCAN;
         if (use_index)
         {
             fill_u32(lc, e.min_pos.ptr, e.w_local, kNoPos);
-            index_search(lc, e.index, batch.sources.ptr, batch.n_sources, e.w_local, e.min_pos.ptr);
+            index_search(lc, e.index, e.g.n, batch.sources.ptr, batch.n_sources, e.w_local, e.min_pos.ptr);
         }
         else
         {
@@ -706,6 +706,7 @@ void ensure_codes(wmh_engine& e)
     ensure_index(e);
     if (e.codes_valid) return;
     if (e.g.n * e.walks_wpv * (u64) e.walks_L >= (1ull << 32)) throw std::domain_error("paired corpus needs walks * walk_length < 2^32 (u64 Szudzik domain)");
+    if (e.index.chunks != 1) throw std::domain_error("paired corpus needs a one-chunk index (local walks * walk length <= 2^31 cells)");
     auto lc = e.lc();
     e.codes.ensure(std::max<u64>(1, e.index.entries));
     compressed_walks_encode(lc, e.index, e.walks.ptr, e.w_local, e.walks_L, e.g.n, e.map, e.codes.ptr);
@@ -1221,7 +1222,7 @@ int wmh_index_find_next(wmh_engine* e, uint32_t vertex, uint64_t walk_id, uint32
         e->bind();
         ensure_index(*e);
         auto lc = e->lc();
-        index_find_next(lc, e->index, e->walks.ptr, e->w_local, e->walks_L, vertex, (u64) local, position, e->small.ptr);
+        index_find_next(lc, e->index, e->g.n, e->walks.ptr, e->w_local, e->walks_L, vertex, (u64) local, position, e->small.ptr);
         u32 r[2];
         WHARF_CUDA(cudaMemcpyAsync(r, e->small.ptr, 8, cudaMemcpyDeviceToHost, e->stream));
         WHARF_CUDA(cudaStreamSynchronize(e->stream));
@@ -1239,10 +1240,12 @@ int wmh_index_size(wmh_engine* e, uint32_t vertex, uint64_t* entries)
     return guarded([&] {
         e->bind();
         ensure_index(*e);
-        u64 p[2];
-        WHARF_CUDA(cudaMemcpyAsync(p, e->index.ptr.ptr + vertex, 16, cudaMemcpyDeviceToHost, e->stream));
+        std::vector<u64> p(2 * (size_t) e->index.chunks);
+        for (u32 c = 0; c < e->index.chunks; c++)
+            WHARF_CUDA(cudaMemcpyAsync(&p[2 * c], e->index.ptr.ptr + (u64) c * (e->g.n + 1) + vertex, 16, cudaMemcpyDeviceToHost, e->stream));
         WHARF_CUDA(cudaStreamSynchronize(e->stream));
-        *entries = p[1] - p[0];
+        *entries = 0;
+        for (u32 c = 0; c < e->index.chunks; c++) *entries += p[2 * c + 1] - p[2 * c];
         return (int) WMH_OK;
     });
 }
@@ -1260,9 +1263,13 @@ int wmh_index_sizes(wmh_engine* e, uint64_t* entries)
         e->bind();
         ensure_index(*e);
         std::vector<u64> ptr(n + 1);
-        WHARF_CUDA(cudaMemcpyAsync(ptr.data(), e->index.ptr.ptr, (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
-        WHARF_CUDA(cudaStreamSynchronize(e->stream));
-        for (u64 v = 0; v < n; v++) entries[v] = ptr[v + 1] - ptr[v];
+        std::fill(entries, entries + n, 0ull);
+        for (u32 c = 0; c < e->index.chunks; c++)
+        {
+            WHARF_CUDA(cudaMemcpyAsync(ptr.data(), e->index.ptr.ptr + (u64) c * (n + 1), (n + 1) * sizeof(u64), cudaMemcpyDeviceToHost, e->stream));
+            WHARF_CUDA(cudaStreamSynchronize(e->stream));
+            for (u64 v = 0; v < n; v++) entries[v] += ptr[v + 1] - ptr[v];
+        }
         return (int) WMH_OK;
     });
 }

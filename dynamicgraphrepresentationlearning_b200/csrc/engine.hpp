@@ -218,14 +218,16 @@ struct DeviceIndex
 {
     bool valid = false;
     u64 entries = 0;                 // stored steps (walk matrix cells holding a vertex)
-    DeviceBuffer<u64> ptr;           // n+1: segment of each vertex in `cells`
-    DeviceBuffer<u32> cells;         // flat cell id = position * W_local + local_walk, ascending per vertex
+    u32 chunks = 1;                  // the corpus is indexed in chunks of whole positions: cell ids stay 32-bit at any size
+    u32 positions_per_chunk = 1;
+    DeviceBuffer<u64> ptr;           // chunks x (n+1): segment of each vertex in `cells`, absolute offsets
+    DeviceBuffer<u32> cells;         // cell id = (position - chunk's first position) * W_local + local_walk, ascending per vertex and chunk
 };
 void index_build(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 n, DeviceIndex& idx);
 // atomicMin of the position of every index entry of every source into min_pos; returns entries visited.
-u64  index_search(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_sources, u64 n_sources, u64 w_local, u32* d_min_pos);
-u64  index_count_touched(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_sources, u64 n_sources);
-void index_find_next(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u32 vertex,
+u64  index_search(const LaunchCtx& lc, const DeviceIndex& idx, u64 n, const u32* d_sources, u64 n_sources, u64 w_local, u32* d_min_pos);
+u64  index_count_touched(const LaunchCtx& lc, const DeviceIndex& idx, u64 n, const u32* d_sources, u64 n_sources);
+void index_find_next(const LaunchCtx& lc, const DeviceIndex& idx, u64 n, const u32* d_walks, u64 w_local, u32 L, u32 vertex,
                      u64 local_walk, u32 position, u32* d_out2 /* [next, found] */);
 void compressed_walks_encode(const LaunchCtx& lc, const DeviceIndex& idx, const u32* d_walks, u64 w_local, u32 L, u64 n,
                              const ShardMap& map, u64* d_codes);

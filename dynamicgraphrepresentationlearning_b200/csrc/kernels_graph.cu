@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(256) aux_invalidate_kernel(const RowDesc* __re
 // the block of the slot v -> c, which arrives with the load that picks c, answers it (94 % of the proposals are no
 // neighbour of prev and the sets are nearly empty: mean 0.28 members at scale-20).  A block is a Bloom filter: extra bits
 // only turn a proof of absence into a "maybe", which the walk kernel resolves with the exact search.
-constexpr u32 kTriChunk = 128;       // slots of one row handled by one warp (four 8-lane groups x 32 slots)
+constexpr u32 kTriChunk = 32;        // slots of one row handled by one warp (four 8-lane groups x 8 slots: hub rows spread over many warps)
 constexpr u32 kTriHeavy = 2048;      // slots whose smaller row is longer than this go to a block of their own
 
 // Scratch of a build: one 16-bit block per edge slot, row v owning blocks[eoff[v], eoff[v] + degree) - the per-row
@@ -379,11 +379,25 @@ __global__ void __launch_bounds__(256) tri_build_kernel(const RowDesc* __restric
         const bool is_heavy = mine && dw.y > kTriHeavy;
         u32 bits = 0, twin = 0xFFFFFFFFu;
         if (mine && !is_heavy)
-            for (u32 k = sub; k < dw.y; k += 8)
+            for (u32 k0 = sub; k0 < dw.y; k0 += 32)               // four elements per lane in flight: the chain x -> filter block is latency
             {
-                const u32 x = __ldg(pool + dw.x + 2 * (u64) k);
-                if (x == u) twin = k;
-                if (tri_member(pool, du, off_u, x, f)) bits |= filter_bits(filter_hash(x));
+                u32 x[4], blk[4];
+#pragma unroll
+                for (u32 j = 0; j < 4; j++) x[j] = k0 + 8 * j < dw.y ? __ldg(pool + dw.x + 2 * (u64) (k0 + 8 * j)) : 0xFFFFFFFFu;
+#pragma unroll
+                for (u32 j = 0; j < 4; j++)
+                    blk[j] = x[j] != 0xFFFFFFFFu ? (u32) f.blocks[off_u + filter_block(filter_hash(x[j]), du.y)] : 0u;
+#pragma unroll
+                for (u32 j = 0; j < 4; j++)
+                {
+                    if (x[j] == u) twin = k0 + 8 * j;
+                    const u32 need = filter_bits(filter_hash(x[j]));
+                    if (x[j] != 0xFFFFFFFFu && (blk[j] & need) == need)
+                    {
+                        const u32 r = lower_bound_row(pool + du.x, du.y, x[j], 1);
+                        if (r < du.y && __ldg(pool + du.x + 2 * (u64) r) == x[j]) bits |= need;
+                    }
+                }
             }
 #pragma unroll
         for (u32 d = 1; d < 8; d <<= 1)

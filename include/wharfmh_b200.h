@@ -227,7 +227,10 @@ WMH_API int wmh_corpus_fingerprint(wmh_engine* e, uint64_t* sum_of_row_hashes);
 
 /* ---- inverted index (walks/inverted_index.h) ----------------------------------------------------- */
 
-/* Builds (or rebuilds) the device index now; batch updates build it lazily when search_mode needs it. */
+/* Builds (or rebuilds) the device index now; batch updates build it lazily when search_mode needs it.  No size cap beyond
+ * memory (4 B per corpus cell + 8 B x (n+1) per chunk + 16 B per cell of one chunk while sorting): corpora of more than 2^31
+ * cells per rank are indexed in chunks of whole positions, so cell ids stay 32-bit (the reference's u32 key walk_id*L+pos
+ * wraps there). */
 WMH_API int wmh_build_index(wmh_engine* e);
 /* InvertedIndex::find_next - walks/inverted_index.h:74-92 on vertex `vertex`: next vertex of walk
  * `walk_id` standing on `vertex` at `position`; WMH_REF_SENTINEL at the last position,

@@ -774,3 +774,45 @@ def test_triangle_filter_symmetry_detection(wharf, wo):
             e.insert_edges_batch(b.copy(), remove_dups=True)
             assert e.neighbour_filter() == want and np.array_equal(e.walks(), o.walks()), name
         o.close()
+
+
+@pytest.mark.parametrize("positions_per_chunk", [1, 4, 7])
+def test_index_in_chunks_of_positions(wharf, wo, positions_per_chunk, monkeypatch):
+    """The inverted index keeps 32-bit cell ids at any corpus size by sorting the corpus in chunks of whole positions
+    (WHARF_INDEX_CHUNK_CELLS forces the chunking a corpus of more than 2^31 cells gets): entry counts, find_next at every
+    position incl. the chunk borders, the INDEX search (affected ids, earliest positions) and the corpora after batches equal
+    the oracle's; the paired corpus (CompressedWalks) asks for a one-chunk index and says so."""
+    rng = np.random.default_rng(5)
+    n, wpv, L = 1 << 9, 3, 19
+    off, adj = wo.rmat_graph(9, 5 * n, seed=2)
+    monkeypatch.setenv("WHARF_INDEX_CHUNK_CELLS", str(positions_per_chunk * n * wpv))
+    o = wo.Oracle(n, off, adj, walks_per_vertex=wpv, walk_length=L)
+    with make(wharf, n, off, adj, walks_per_vertex=wpv, walk_length=L, search_mode=wharf.SEARCH_INDEX) as e:
+        assert e.generate_initial_random_walks() == o.generate()
+        ref = o.walks()
+        sizes = np.bincount(ref[ref != wo.NO_VERTEX].astype(np.int64), minlength=n)
+        assert np.array_equal(e.index_sizes(), sizes)
+        for v in (0, 1, 200, n - 1):
+            assert e.index_size(v) == sizes[v]
+        for w in (0, 5, n + 3, n * wpv - 1):
+            for p in range(L):
+                v = ref[w, p]
+                if v == wo.NO_VERTEX:
+                    break
+                nxt, found = e.find_next(int(v), w, p)
+                expect = wharf.REF_SENTINEL if (p == L - 1 or ref[w, p + 1] == wo.NO_VERTEX) else int(ref[w, p + 1])
+                assert found and nxt == expect, (w, p)
+                assert not e.find_next((int(v) + 1) % n, w, p)[1] or ref[w, p] == (int(v) + 1) % n
+        for step in range(4):
+            b = random_batch(rng, n, 30 + 10 * step)
+            delete = step == 2
+            o.update(b.copy(), delete=delete, remove_dups=True)
+            (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
+            assert e.last_search_mode() == wharf.SEARCH_INDEX
+            ids, pos = e.affected_walks()
+            assert np.array_equal(ids, o.affected()[0]) and np.array_equal(pos, o.affected()[1])
+            assert np.array_equal(e.walks(), o.walks())
+        ref = o.walks()
+        assert np.array_equal(e.index_sizes(), np.bincount(ref[ref != wo.NO_VERTEX].astype(np.int64), minlength=n))
+        with pytest.raises(wharf.WharfError):
+            e.compressed_walks()

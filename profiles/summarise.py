@@ -2,6 +2,9 @@
 into the text summaries committed under profiles/.  Usage:
     python profiles/summarise.py launches gpurun_out/launches.csv > profiles/rNN_launches.txt
     python profiles/summarise.py kernel   gpurun_out/prof_walk.ncu-rep > profiles/rNN_walk_kernel.txt
+    python profiles/summarise.py traffic  gpurun_out/traffic.csv [key] > profiles/rNN_traffic.txt
+        (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum: DRAM bytes per kernel of one pass;
+         with a key such as dw25:8 the totals are also written into profiles/roofline_traffic.json)
 """
 import collections
 import csv
@@ -54,5 +57,45 @@ def kernel(path):
         print()
 
 
+def traffic(path, key=None):
+    import json
+    import pathlib
+    lines = [l for l in open(path) if not l.startswith("==")]
+    rows = [r for r in csv.reader(lines) if len(r) > 5]
+    hdr = rows[0]
+    i_id, i_name, i_metric, i_val, i_unit = hdr.index("ID"), hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    scale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    agg = collections.defaultdict(lambda: {"n": set(), "ms": 0.0, "read": 0.0, "write": 0.0})
+    for r in rows[1:]:
+        try:
+            v = float(r[i_val].replace(",", "")) * scale.get(r[i_unit], 1.0)
+        except ValueError:
+            continue
+        a = agg[r[i_name][:100]]
+        a["n"].add(r[i_id])
+        if r[i_metric] == "gpu__time_duration.sum":
+            a["ms"] += v
+        elif r[i_metric] == "dram__bytes_read.sum":
+            a["read"] += v
+        elif r[i_metric] == "dram__bytes_write.sum":
+            a["write"] += v
+    ms = sum(a["ms"] for a in agg.values())
+    rd = sum(a["read"] for a in agg.values())
+    wr = sum(a["write"] for a in agg.values())
+    print(f"# {path}: {sum(len(a['n']) for a in agg.values())} launches; per-launch times are serialised and cold-cache (compare shares)")
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
+        gbs = (a["read"] + a["write"]) / a["ms"] / 1e6 if a["ms"] else 0.0
+        print(f"{a['ms']:9.3f} ms x{len(a['n']):<4d} read {a['read'] / 1e9:8.2f} GB  write {a['write'] / 1e9:8.2f} GB  {gbs:7.0f} GB/s  {k}")
+    print(f"# total: {ms:.3f} ms serialised, read {rd / 1e9:.2f} GB + write {wr / 1e9:.2f} GB = {(rd + wr) / 1e9:.2f} GB per pass")
+    if key:
+        f = pathlib.Path(__file__).with_name("roofline_traffic.json")
+        data = json.loads(f.read_text())
+        data[key] = {"read": rd, "write": wr, "pass_kernel_ms_serialised": round(ms, 3),
+                     "source": f"ncu dram__bytes_read.sum + dram__bytes_write.sum over the kernels of one generate pass of rank 0's shard (tools/profile_pass.py "
+                               f"{key.split(':')[0]} <mode> 0 {key.split(':')[1]} on one GPU; MH shards without the peer exchange: every sampler init is "
+                               f"computed locally, an upper bound of a rank's traffic)"}
+        f.write_text(json.dumps(data, indent=1) + "\n")
+
+
 if __name__ == "__main__":
-    {"launches": launches, "kernel": kernel}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "kernel": kernel, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])

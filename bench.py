@@ -360,8 +360,14 @@ def roofline_for(ctx, name, spec, n, m, d_offsets, engine, local_steps_per_pass,
         out["frac"] = out["achieved"] / ctx.peak_gbs
         out["bytes_per_step_measured"] = traffic / local_steps_per_pass
     else:
-        out.update({"achieved": algorithmic_gbs, "traffic": None, "frac": algorithmic_gbs / ctx.peak_gbs,
-                    "definition": "no ncu capture for this workload / world size: achieved falls back to the SURVEY 8d algorithmic bytes"})
+        frac = algorithmic_gbs / ctx.peak_gbs
+        if frac <= 1.0:
+            out.update({"achieved": algorithmic_gbs, "traffic": None, "frac": frac,
+                        "definition": "no ncu capture for this workload / world size: achieved falls back to the SURVEY 8d algorithmic bytes"})
+        else:       # the model does not describe what ran (L2-resident graph, or rows fetched once for many walkers): no HBM fraction is claimed
+            out.update({"achieved": None, "traffic": None, "frac": None,
+                        "definition": "no ncu capture for this workload / world size, and the SURVEY 8d algorithmic bytes exceed what HBM can move in the "
+                                      "measured time (cached rows): no HBM fraction claimed; see `algorithmic`"})
     if spec["det"]:
         corpus_bytes = float(engine.number_of_local_walks()) * LEN * 4
         floor_ms = corpus_bytes / (ctx.peak_gbs * 1e9) * 1e3

@@ -43,7 +43,8 @@ struct Trace
         if (!mode) return;
         if (mode == 1) cudaStreamSynchronize(stream);
         const auto t1 = std::chrono::steady_clock::now();
-        std::fprintf(stderr, "[wharf trace] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        const char* rank = std::getenv("RANK");
+        std::fprintf(stderr, "[wharf trace%s%s] %-28s %9.3f ms\n", rank ? " r" : "", rank ? rank : "", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
         t0 = t1;
     }
 };

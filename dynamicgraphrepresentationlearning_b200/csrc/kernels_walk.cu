@@ -1116,6 +1116,7 @@ void peer_barrier(const LaunchCtx& lc, PeerLink& link)
 void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, PeerLink& link)
 {
     const u32 n = (u32) wp.n;
+    Trace tr(lc.stream);
     Scratch<u32> eoff(lc.stream, (u64) n + 1), split(lc.stream, kPeerMaxWorld + 1);
     {
         cub::CountingInputIterator<u32> iota(0);
@@ -1132,12 +1133,16 @@ void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, Pe
     const unsigned grid = (unsigned) std::min<u64>(div_up(chunks * 32, kWalkBlock), (u64) lc.sm_count * 8);
     n2v_share_init_kernel<<<grid, kWalkBlock, 0, lc.stream>>>(p, eoff.ptr, split.ptr, link.ptrs, link.world, link.rank);
     lc.count(2);
+    tr.mark("share: scan + splits + init kernel");
     peer_barrier(lc, link);                                    // every rank's words have arrived
+    tr.mark("share: barrier (words arrived)");
     n2v_share_import_kernel<<<div_up((u64) n * 8, 256), 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, split.ptr,
                                                                              reinterpret_cast<unsigned short*>(link.own() + kPeerFlagBytes), n, link.rank,
                                                                              reinterpret_cast<const u32*>(link.own() + kPeerErrorOffset));
     lc.count();
+    tr.mark("share: import");
     peer_barrier(lc, link);                                    // nobody overwrites a buffer that is still being read
+    tr.mark("share: barrier (windows free)");
     WHARF_CUDA(cudaGetLastError());
     ++link.exchanges;
 }

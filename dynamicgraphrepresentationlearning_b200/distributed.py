@@ -117,14 +117,16 @@ class ShardedWharfMH:
         parts = [gathered[r * width: r * width + int(counts[r].item())] for r in range(self.world)]
         return np.sort(torch.cat(parts).cpu().numpy().astype(np.uint64))
 
-    def warm_collectives(self) -> None:
-        """One untimed round of the collectives an update uses (broadcast, all-gather, device sort): NCCL opens its channels
-        for each collective kind on first use (71 ms for the first all-gather at N = 2), which is set-up, not batch latency."""
+    def warm_collectives(self, ids_per_rank: int = 4) -> None:
+        """One untimed round of the collectives an update uses (broadcast, all-gather of `ids_per_rank` ids, device sort): NCCL
+        opens its channels for each collective kind on first use and sizes its buffers on the first large message (71 ms for
+        the first all-gather at N = 2, 20 ms for the first 80 MB one at N = 8), which is set-up, not batch latency."""
         count = torch.zeros(1, dtype=torch.int64, device=self.device)
         dist.broadcast(count, src=0, group=self.group)
         pairs = torch.zeros((16, 2), dtype=torch.int32, device=self.device)
         dist.broadcast(pairs, src=0, group=self.group)
-        ids = torch.arange(4, dtype=torch.int64, device=self.device) + 4 * self.rank
+        ids_per_rank = max(1, int(ids_per_rank))
+        ids = torch.arange(ids_per_rank, dtype=torch.int64, device=self.device) + ids_per_rank * self.rank
         if self._on_gpu:
             self.all_gather_ids_device(ids)
             torch.cuda.synchronize(self.device)

@@ -778,23 +778,46 @@ __global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParam
 // Eight lanes per row: tails of the rows other ranks computed <- the words they stored into the own exchange buffer.
 // A barrier that gave up waiting (error word set) means the window may hold words of an earlier pass or only part of
 // this one: the caches are then left EMPTY (0 = lazy first-touch init in the walk kernel) instead of imported.  Every
-// word is zeroed once read, so a later pass can never import a stale valid entry either.
+// word is zeroed once read, so a later pass can never import a stale valid entry either.  The group takes the first
+// kImportHead elements of its row; longer rows are listed and finished by a block each (a hub row of 13 K neighbours
+// behind eight lanes was 1.1 ms of a 4.5 ms pass on eight GPUs).
+constexpr u32 kImportHead = 256;
+
+__device__ __forceinline__ void import_words(unsigned short* __restrict__ src, unsigned short* __restrict__ halves, u32 first, u32 last, u32 lane, u32 lanes,
+                                             bool failed)
+{
+    for (u32 i = first + lane; i < last; i += lanes)
+    {
+        const unsigned short word = src[i];
+        src[i] = 0;
+        halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : word;                          // low half of aux word i = halves[4 i + 2]
+    }
+}
+
 __global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
                                                                const u32* __restrict__ split, unsigned short* __restrict__ received, u32 n, u32 rank,
-                                                               const u32* __restrict__ error_word)
+                                                               const u32* __restrict__ error_word, u32* __restrict__ long_rows, u32* __restrict__ n_long)
 {
     const u64 t = (u64) blockIdx.x * 256 + threadIdx.x;
     const u32 v = (u32) (t >> 3), sub = threadIdx.x & 7;
     if (v >= n || (v >= split[rank] && v < split[rank + 1])) return;
     const bool failed = *reinterpret_cast<const volatile u32*>(error_word) != 0;
     const RowDesc d = load_desc(desc, v);
-    unsigned short* src = received + __ldg(eoff + v);
-    unsigned short* halves = reinterpret_cast<unsigned short*>(pool + d.begin);                // low half of aux word i = halves[4 i + 2]
-    for (u32 i = sub; i < d.degree; i += 8)
+    import_words(received + __ldg(eoff + v), reinterpret_cast<unsigned short*>(pool + d.begin), 0, min(d.degree, kImportHead), sub, 8, failed);
+    if (sub == 0 && d.degree > kImportHead) long_rows[atomicAdd(n_long, 1u)] = v;
+}
+
+__global__ void __launch_bounds__(256) n2v_share_import_long_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
+                                                                    unsigned short* __restrict__ received, const u32* __restrict__ error_word,
+                                                                    const u32* __restrict__ long_rows, const u32* __restrict__ n_long)
+{
+    const bool failed = *reinterpret_cast<const volatile u32*>(error_word) != 0;
+    const u32 count = *n_long;
+    for (u32 j = blockIdx.x; j < count; j += gridDim.x)
     {
-        const unsigned short word = src[i];
-        src[i] = 0;
-        halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : word;
+        const u32 v = long_rows[j];
+        const RowDesc d = load_desc(desc, v);
+        import_words(received + __ldg(eoff + v), reinterpret_cast<unsigned short*>(pool + d.begin), kImportHead, d.degree, threadIdx.x, 256, failed);
     }
 }
 
@@ -1136,10 +1159,16 @@ void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, Pe
     tr.mark("share: scan + splits + init kernel");
     peer_barrier(lc, link);                                    // every rank's words have arrived
     tr.mark("share: barrier (words arrived)");
-    n2v_share_import_kernel<<<div_up((u64) n * 8, 256), 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, split.ptr,
-                                                                             reinterpret_cast<unsigned short*>(link.own() + kPeerFlagBytes), n, link.rank,
-                                                                             reinterpret_cast<const u32*>(link.own() + kPeerErrorOffset));
-    lc.count();
+    {
+        Scratch<u32> long_rows(lc.stream, m / kImportHead + 2);                 // rows longer than kImportHead: at most m / kImportHead of them
+        WHARF_CUDA(cudaMemsetAsync(long_rows.ptr, 0, 4, lc.stream));            // [0] = their count
+        unsigned short* received = reinterpret_cast<unsigned short*>(link.own() + kPeerFlagBytes);
+        const u32* error_word = reinterpret_cast<const u32*>(link.own() + kPeerErrorOffset);
+        n2v_share_import_kernel<<<div_up((u64) n * 8, 256), 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, split.ptr, received, n, link.rank, error_word,
+                                                                                 long_rows.ptr + 1, long_rows.ptr);
+        n2v_share_import_long_kernel<<<lc.sm_count * 8, 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, received, error_word, long_rows.ptr + 1, long_rows.ptr);
+        lc.count(2);
+    }
     tr.mark("share: import");
     peer_barrier(lc, link);                                    // nobody overwrites a buffer that is still being read
     tr.mark("share: barrier (windows free)");

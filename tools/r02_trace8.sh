@@ -2,6 +2,7 @@
 # round 2: where the per-pass fixed cost of the MH peer exchange goes at N ranks (WHARF_TRACE=1: stream synchronised at every mark)
 N=${1:-8}
 mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_peer_exchange.py -x -q -m gpu > gpurun_out/o_peer_pytest.log 2>&1; tail -2 gpurun_out/o_peer_pytest.log
 WHARF_TRACE=1 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N \
   --workload n2v20 --steps 3 --warmup 2 --no-e2e --no-cpu-baseline --no-index-vs-scan --updates 1 > gpurun_out/o_trace_$N.json 2> gpurun_out/o_trace_$N.err
 echo rc=$?

@@ -783,15 +783,21 @@ __global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParam
 // behind eight lanes was 1.1 ms of a 4.5 ms pass on eight GPUs).
 constexpr u32 kImportHead = 256;
 
+__device__ u32 g_import_probe = 0;      // TEMPORARY measurement switch: bit 0 = do not zero the window, bit 1 = do not store the halves
+
 __device__ __forceinline__ void import_words(unsigned short* __restrict__ src, unsigned short* __restrict__ halves, u32 first, u32 last, u32 lane, u32 lanes,
                                              bool failed)
 {
+    const u32 probe = g_import_probe;
+    u32 sink = 0;
     for (u32 i = first + lane; i < last; i += lanes)
     {
         const unsigned short word = src[i];
-        src[i] = 0;
-        halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : word;                          // low half of aux word i = halves[4 i + 2]
+        if (!(probe & 1)) src[i] = 0;
+        if (!(probe & 2)) halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : word;        // low half of aux word i = halves[4 i + 2]
+        else sink += word;
     }
+    if (sink == 0xFFFFFFFFu) halves[2] = 0;
 }
 
 __global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
@@ -1160,6 +1166,11 @@ void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, Pe
     peer_barrier(lc, link);                                    // every rank's words have arrived
     tr.mark("share: barrier (words arrived)");
     {
+        if (const char* env = std::getenv("WHARF_IMPORT_PROBE"))
+        {
+            const u32 v = (u32) std::atoi(env);
+            WHARF_CUDA(cudaMemcpyToSymbolAsync(g_import_probe, &v, 4, 0, cudaMemcpyHostToDevice, lc.stream));
+        }
         Scratch<u32> long_rows(lc.stream, m / kImportHead + 2);                 // rows longer than kImportHead: at most m / kImportHead of them
         WHARF_CUDA(cudaMemsetAsync(long_rows.ptr, 0, 4, lc.stream));            // [0] = their count
         unsigned short* received = reinterpret_cast<unsigned short*>(link.own() + kPeerFlagBytes);

@@ -777,31 +777,23 @@ __global__ void __launch_bounds__(kWalkBlock) n2v_share_init_kernel(DevWalkParam
 
 // Eight lanes per row: tails of the rows other ranks computed <- the words they stored into the own exchange buffer.
 // A barrier that gave up waiting (error word set) means the window may hold words of an earlier pass or only part of
-// this one: the caches are then left EMPTY (0 = lazy first-touch init in the walk kernel) instead of imported.  Every
-// word is zeroed once read, so a later pass can never import a stale valid entry either.  The group takes the first
-// kImportHead elements of its row; longer rows are listed and finished by a block each (a hub row of 13 K neighbours
-// behind eight lanes was 1.1 ms of a 4.5 ms pass on eight GPUs).
+// this one: the caches are then left EMPTY (0 = lazy first-touch init in the walk kernel) instead of imported.  After a
+// barrier that succeeded every word read here is fresh: each exchange overwrites every state of the current graph in
+// every window (state e is stored by the rank that owns it), so nothing of an earlier pass can survive into an import.
+// (Zeroing each word after reading it, as a second line of defence, cost 0.5 ms at two ranks and 0.9 ms at eight: the
+// owner's 2-byte stores into its peer-mapped window are slow; measured with tools/r02_import_probe.sh.)  The group takes
+// the first kImportHead elements of its row; longer rows are listed and finished by a block each.
 constexpr u32 kImportHead = 256;
 
-__device__ u32 g_import_probe = 0;      // TEMPORARY measurement switch: bit 0 = do not zero the window, bit 1 = do not store the halves
-
-__device__ __forceinline__ void import_words(unsigned short* __restrict__ src, unsigned short* __restrict__ halves, u32 first, u32 last, u32 lane, u32 lanes,
-                                             bool failed)
+__device__ __forceinline__ void import_words(const unsigned short* __restrict__ src, unsigned short* __restrict__ halves, u32 first, u32 last, u32 lane,
+                                             u32 lanes, bool failed)
 {
-    const u32 probe = g_import_probe;
-    u32 sink = 0;
     for (u32 i = first + lane; i < last; i += lanes)
-    {
-        const unsigned short word = src[i];
-        if (!(probe & 1)) src[i] = 0;
-        if (!(probe & 2)) halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : word;        // low half of aux word i = halves[4 i + 2]
-        else sink += word;
-    }
-    if (sink == 0xFFFFFFFFu) halves[2] = 0;
+        halves[4 * (u64) i + 2] = failed ? (unsigned short) 0 : src[i];                        // low half of aux word i = halves[4 i + 2]
 }
 
 __global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
-                                                               const u32* __restrict__ split, unsigned short* __restrict__ received, u32 n, u32 rank,
+                                                               const u32* __restrict__ split, const unsigned short* __restrict__ received, u32 n, u32 rank,
                                                                const u32* __restrict__ error_word, u32* __restrict__ long_rows, u32* __restrict__ n_long)
 {
     const u64 t = (u64) blockIdx.x * 256 + threadIdx.x;
@@ -814,7 +806,7 @@ __global__ void __launch_bounds__(256) n2v_share_import_kernel(const RowDesc* __
 }
 
 __global__ void __launch_bounds__(256) n2v_share_import_long_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const u32* __restrict__ eoff,
-                                                                    unsigned short* __restrict__ received, const u32* __restrict__ error_word,
+                                                                    const unsigned short* __restrict__ received, const u32* __restrict__ error_word,
                                                                     const u32* __restrict__ long_rows, const u32* __restrict__ n_long)
 {
     const bool failed = *reinterpret_cast<const volatile u32*>(error_word) != 0;
@@ -1166,14 +1158,9 @@ void n2v_share_sampler_init(const LaunchCtx& lc, const WalkParams& wp, u64 m, Pe
     peer_barrier(lc, link);                                    // every rank's words have arrived
     tr.mark("share: barrier (words arrived)");
     {
-        if (const char* env = std::getenv("WHARF_IMPORT_PROBE"))
-        {
-            const u32 v = (u32) std::atoi(env);
-            WHARF_CUDA(cudaMemcpyToSymbolAsync(g_import_probe, &v, 4, 0, cudaMemcpyHostToDevice, lc.stream));
-        }
         Scratch<u32> long_rows(lc.stream, m / kImportHead + 2);                 // rows longer than kImportHead: at most m / kImportHead of them
         WHARF_CUDA(cudaMemsetAsync(long_rows.ptr, 0, 4, lc.stream));            // [0] = their count
-        unsigned short* received = reinterpret_cast<unsigned short*>(link.own() + kPeerFlagBytes);
+        const unsigned short* received = reinterpret_cast<const unsigned short*>(link.own() + kPeerFlagBytes);
         const u32* error_word = reinterpret_cast<const u32*>(link.own() + kPeerErrorOffset);
         n2v_share_import_kernel<<<div_up((u64) n * 8, 256), 256, 0, lc.stream>>>(wp.desc, wp.pool_rw, eoff.ptr, split.ptr, received, n, link.rank, error_word,
                                                                                  long_rows.ptr + 1, long_rows.ptr);

@@ -361,7 +361,7 @@ def roofline_for(ctx, name, spec, n, m, d_offsets, engine, local_steps_per_pass,
         out["bytes_per_step_measured"] = traffic / local_steps_per_pass
     else:
         frac = algorithmic_gbs / ctx.peak_gbs
-        if frac <= 1.0:
+        if frac <= 1.0 and n * 8 + m * 4 > (126 << 20):      # an L2-resident graph is no HBM workload at any rate
             out.update({"achieved": algorithmic_gbs, "traffic": None, "frac": frac,
                         "definition": "no ncu capture for this workload / world size: achieved falls back to the SURVEY 8d algorithmic bytes"})
         else:       # the model does not describe what ran (L2-resident graph, or rows fetched once for many walkers): no HBM fraction is claimed

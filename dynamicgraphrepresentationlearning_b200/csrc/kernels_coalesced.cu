@@ -95,12 +95,33 @@ __global__ void __launch_bounds__(kBlock) coalesced_init_kernel(u32* __restrict_
     row0[i] = v;
 }
 
+// First step of every walker of up to kFirstReplicas WHOLE replicas at once: walker i of such a replica starts on vertex
+// i, so at position 0 all of them read the same descriptor and the same row - one thread per vertex loads them once and
+// writes corpus row 1 of each replica (cell = N(i)[X[r][0] % deg]), which the replica's first advance then reads instead
+// of the graph (ten replicas: ten sweeps over the 2.4 GB adjacency become one; scale-25: 71.0 -> 68 ms).
+constexpr u32 kFirstReplicas = 16;
+struct FirstDraws { u64 x[kFirstReplicas]; };
+
+__global__ void __launch_bounds__(kBlock) coalesced_first_steps_kernel(const RowDesc* __restrict__ desc, const u32* __restrict__ pool, u32 n, u32 shift,
+                                                                       FirstDraws draws, u32 replicas, u32* __restrict__ row1, u64 replica_stride)
+{
+    const u32 v = blockIdx.x * kBlock + threadIdx.x;
+    if (v >= n) return;
+    const RowDesc d = ld_desc(desc, v);
+#pragma unroll 4
+    for (u32 r = 0; r < replicas; r++)
+    {
+        const u32 u = d.degree ? __ldg(pool + d.begin + ((u64) mod_u64_u32(draws.x[r], d.degree) << shift)) : kNoVertex;
+        __stcs(row1 + (u64) r * replica_stride + v, u);
+    }
+}
+
 // record[c][j] = vertex of class c after j + 1 steps from cv[c], j < k; a class on a degree-0 vertex (isolated
 // start or sink) turns into kNoVertex and stays there.  The final vertex is marked for the merge.
 template <u32 R>
 __global__ void __launch_bounds__(kBlock) coalesced_advance_kernel(const RowDesc* __restrict__ desc, const u32* __restrict__ pool, const u32* __restrict__ cv,
                                                                    const u32* __restrict__ n_classes, SegDraws draws, u32 k, u32* __restrict__ rec,
-                                                                   u32* __restrict__ bitmap, u32 shift)
+                                                                   u32* __restrict__ bitmap, u32 shift, const u32* __restrict__ first_step)
 {
     const u32 nc = *n_classes;
     for (u32 c = blockIdx.x * kBlock + threadIdx.x; c < nc; c += gridDim.x * kBlock)
@@ -110,7 +131,8 @@ __global__ void __launch_bounds__(kBlock) coalesced_advance_kernel(const RowDesc
 #pragma unroll
         for (u32 j = 0; j < R - 1; j++)
         {
-            if (j < k && u != kNoVertex)
+            if (j == 0 && first_step) u = __ldcs(first_step + c);          // the replica's first segment: class c = walker c (coalesced_first_steps_kernel)
+            else if (j < k && u != kNoVertex)
             {
                 const RowDesc d = ld_desc(desc, u);
                 u = d.degree ? __ldg(pool + d.begin + ((u64) mod_u64_u32(draws.x[j], d.degree) << shift)) : kNoVertex;
@@ -334,10 +356,12 @@ bool force_library_scan()
 
 template <u32 R>
 void run_segment(const SegmentCtx& s, const SegDraws& draws, u32 k, const u32* cv, u32* cv_next, const u32* nc, u32* nc_next, u32* first_row, u32 stored,
-                 bool merge)
+                 bool merge, const u32* first_step = nullptr)
 {
     const LaunchCtx& lc = s.lc;
-    coalesced_advance_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.wp.desc, s.wp.pool, cv, nc, draws, k, s.rec, merge ? s.bitmap : nullptr, s.wp.shift);
+    coalesced_advance_kernel<R><<<s.class_grid, kBlock, 0, lc.stream>>>(s.wp.desc, s.wp.pool, cv, nc, draws, k, s.rec, merge ? s.bitmap : nullptr, s.wp.shift,
+                                                                        first_step);
+    if (first_step) stored = 0;                               // the segment's only row is the array just read
     lc.count();
     if (merge)
     {
@@ -482,6 +506,7 @@ struct ReplicaJob
     u32 nl;           // walkers
     u64 first;        // first local walk = column offset in every corpus row
     u32 rank, world;  // start vertex of walker i: shard_start(i, rank, world, n)
+    bool row1_done = false;   // corpus row 1 of this (whole) replica was written by coalesced_first_steps_kernel
 };
 
 std::vector<ReplicaJob> replica_jobs(const ShardMap& m)
@@ -513,9 +538,10 @@ void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_
         const u32 stored = std::min(k, L - 1 - a);            // cells a + 1 .. a + stored exist; the last draw is only counted
         const bool merge = a + k < L;
         u32* first_row = col + (u64) (a + 1) * wp.w_local;
+        const u32* first_step = (a == 0 && job.row1_done && k == 1 && stored == 1) ? first_row : nullptr;
         switch (R)
         {
-            case 2: run_segment<2>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
+            case 2: run_segment<2>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge, first_step); break;
             case 4: run_segment<4>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
             default: run_segment<8>(s, draws, k, cv, cv_next, nc, nc_next, first_row, stored, merge); break;
         }
@@ -525,12 +551,39 @@ void enqueue_replica(const LaunchCtx& lc, const WalkParams& wp, const u64* host_
     WHARF_CUDA(cudaGetLastError());
 }
 
+// Row 1 of every whole replica in one sweep over the graph (two or more of them, walks of at least two positions).
+void enqueue_first_steps(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, std::vector<ReplicaJob>& jobs)
+{
+    const char* env = std::getenv("WHARF_FIRST_STEPS");
+    if (wp.L < 2 || (env && std::atoi(env) == 0)) return;
+    std::vector<ReplicaJob*> whole;
+    for (ReplicaJob& job : jobs)
+        if (job.world == 1 && job.nl == wp.n) whole.push_back(&job);
+    if (whole.size() < 2) return;
+    for (size_t g = 0; g < whole.size(); g += kFirstReplicas)
+    {
+        const u32 count = (u32) std::min<size_t>(kFirstReplicas, whole.size() - g);
+        FirstDraws draws{};
+        for (u32 r = 0; r < count; r++)
+        {
+            draws.x[r] = host_draw[(u64) whole[g + r]->replica * wp.L];
+            if (whole[g + r]->first != whole[g]->first + (u64) r * wp.n) return;      // whole replicas lie side by side (ShardMap); anything else: no fusion
+        }
+        coalesced_first_steps_kernel<<<div_up(wp.n, kBlock), kBlock, 0, lc.stream>>>(wp.desc, wp.pool, (u32) wp.n, wp.shift, draws, count,
+                                                                                  wp.walks + wp.w_local + whole[g]->first, wp.n);
+        lc.count();
+        for (u32 r = 0; r < count; r++) whole[g + r]->row1_done = true;
+    }
+    WHARF_CUDA(cudaGetLastError());
+}
+
 // One replica after the other on the caller's stream.
 void enqueue_serial(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
-                    const std::vector<ReplicaJob>& jobs, const std::function<void(u64, u64)>& after_replica)
+                    std::vector<ReplicaJob>& jobs, const std::function<void(u64, u64)>& after_replica)
 {
     const CoalescedBranch& b = pl.branch[0];
     WHARF_CUDA(cudaMemsetAsync(b.bitmap.ptr, 0, (u64) pl.words * 4, lc.stream));
+    enqueue_first_steps(lc, wp, host_draw, jobs);
     for (const ReplicaJob& job : jobs)
     {
         enqueue_replica(lc, wp, host_draw, d_steps, pl, b, job);
@@ -540,8 +593,9 @@ void enqueue_serial(const LaunchCtx& lc, const WalkParams& wp, const u64* host_d
 
 // Inside a stream capture: job j on branch j % branches; the extra branches fork from and join the caller's stream.
 void enqueue_forked(const LaunchCtx& lc, const WalkParams& wp, const u64* host_draw, unsigned long long* d_steps, CoalescedPlan& pl,
-                    const std::vector<ReplicaJob>& jobs, u32 branches)
+                    std::vector<ReplicaJob>& jobs, u32 branches)
 {
+    enqueue_first_steps(lc, wp, host_draw, jobs);
     WHARF_CUDA(cudaEventRecord(pl.fork, lc.stream));
     for (u32 i = 0; i < branches; i++)
     {
@@ -570,7 +624,7 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
 {
     if (wp.w_local == 0) return;
     const u32 words = (u32) ((wp.n + 31) / 32);
-    const std::vector<ReplicaJob> jobs = replica_jobs(wp.map);
+    std::vector<ReplicaJob> jobs = replica_jobs(wp.map);
     u32 nl_max = 0;
     for (const ReplicaJob& job : jobs) nl_max = std::max(nl_max, job.nl);
     CoalescedPlan local;

@@ -552,7 +552,7 @@ def test_keyed_mh_directed_batches_vs_oracle(wharf, wo, init):
             assert np.array_equal(e.walks(), o.walks()), f"corpus differs after directed batch {step}"
 
 
-@pytest.mark.parametrize("case", ["rmat10", "rmat12_sparse", "directed_sinks", "short", "single"])
+@pytest.mark.parametrize("case", ["rmat10", "rmat12_sparse", "directed_sinks", "short", "many_replicas", "single"])
 def test_coalesced_generation_equals_oracle(wharf, wo, case):
     """GENERATE_COALESCED (step-synchronous, walkers of a replica that met advance once) must give the corpus and
     step count of the oracle and of the one-walker-per-thread kernel, including isolated starts, sinks of a
@@ -573,6 +573,9 @@ def test_coalesced_generation_equals_oracle(wharf, wo, case):
     elif case == "short":
         n, wpv, L = 1 << 9, 3, 2
         off, adj = wo.rmat_graph(9, 3000)
+    elif case == "many_replicas":                              # more whole replicas than one fused first-step launch takes (16)
+        n, wpv, L = 1 << 9, 37, 6
+        off, adj = wo.rmat_graph(9, 2500, seed=4)
     else:
         n, wpv, L = 1 << 9, 1, 1
         off, adj = wo.rmat_graph(9, 3000)
@@ -602,10 +605,11 @@ def test_coalesced_generation_equals_oracle(wharf, wo, case):
         assert np.array_equal(full, o2.walks())
 
 
-@pytest.mark.parametrize("knobs", [{"WHARF_RANK_SCAN": "1"}, {"WHARF_GRAPH": "0"}, {"WHARF_BRANCHES": "1"}, {"WHARF_BRANCHES": "7"}])
+@pytest.mark.parametrize("knobs", [{"WHARF_RANK_SCAN": "1"}, {"WHARF_GRAPH": "0"}, {"WHARF_BRANCHES": "1"}, {"WHARF_BRANCHES": "7"}, {"WHARF_FIRST_STEPS": "0"}])
 def test_coalesced_schedule_variants(wharf, wo, knobs, monkeypatch):
     """The corpus does not depend on how the coalesced pass is scheduled: library-scan ranking (the path for more than
-    134 M vertices), plain launches instead of the captured CUDA graph, one or many parallel graph branches."""
+    134 M vertices), plain launches instead of the captured CUDA graph, one or many parallel graph branches, the first step of
+    the whole replicas taken per replica instead of in one sweep."""
     for k, v in knobs.items():
         monkeypatch.setenv(k, v)
     n = 1 << 11

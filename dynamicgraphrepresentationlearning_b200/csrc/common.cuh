@@ -129,6 +129,27 @@ __device__ __forceinline__ u32 mod_u64_u32(u64 x, u32 d)
     return (u32) rem;
 }
 
+// The same remainder for several x and ONE divisor: inv = 1.0 / d computed once (reciprocal_of), each reduction is then two
+// double multiplications instead of an integer modulo and a double division.  Exact: both quotient estimates are within
+// 2^-19 of the true quotient (hi < 2^32 and t < d * 2^32 carry at most 2^-52 of relative error through the product),
+// so truncation lands on the true quotient or one beside it, and the two corrections below restore the remainder.
+__device__ __forceinline__ double reciprocal_of(u32 d) { return __drcp_rn((double) d); }
+
+__device__ __forceinline__ u32 mod_u64_u32_rcp(u64 x, u32 d, double inv)
+{
+    const u32 hi = (u32) (x >> 32);
+    const u32 q1 = __double2uint_rz(__dmul_rz((double) hi, inv));
+    i64 r1 = (i64) hi - (i64) ((u64) q1 * d);
+    if (r1 < 0) r1 += d;
+    if (r1 >= (i64) d) r1 -= d;
+    const u64 t = ((u64) r1 << 32) | (u32) x;                  // < d * 2^32
+    const u64 q = __double2ull_rz(__dmul_rz(__ull2double_rz(t), inv));
+    i64 rem = (i64) (t - q * (u64) d);
+    if (rem < 0) rem += d;
+    if (rem >= (i64) d) rem -= d;
+    return (u32) rem;
+}
+
 __device__ __forceinline__ u32 warp_sum(u32 v)
 {
 #pragma unroll

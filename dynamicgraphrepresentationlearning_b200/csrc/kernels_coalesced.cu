@@ -108,10 +108,11 @@ __global__ void __launch_bounds__(kBlock) coalesced_first_steps_kernel(const Row
     const u32 v = blockIdx.x * kBlock + threadIdx.x;
     if (v >= n) return;
     const RowDesc d = ld_desc(desc, v);
+    const double inv = d.degree ? reciprocal_of(d.degree) : 0.0;
 #pragma unroll 4
     for (u32 r = 0; r < replicas; r++)
     {
-        const u32 u = d.degree ? __ldg(pool + d.begin + ((u64) mod_u64_u32(draws.x[r], d.degree) << shift)) : kNoVertex;
+        const u32 u = d.degree ? __ldg(pool + d.begin + ((u64) mod_u64_u32_rcp(draws.x[r], d.degree, inv) << shift)) : kNoVertex;
         __stcs(row1 + (u64) r * replica_stride + v, u);
     }
 }

@@ -348,8 +348,9 @@ __device__ __forceinline__ InitValue n2v_init_weight_group(const DevWalkParams& 
     {
         const u64 key_b = ((u64) prev << 32) | __ldg(p.version + cur);
         u32 slot[3], x[3], fh[3], fw[3];
+        const double inv = reciprocal_of(dcur.degree);       // three proposals, one divisor
 #pragma unroll
-        for (u32 k = 0; k < 3; k++) slot[k] = mod_u64_u32(keyed_draw(p.seed, kDomSampler, cur, key_b, sub + 8 * k), dcur.degree);
+        for (u32 k = 0; k < 3; k++) slot[k] = mod_u64_u32_rcp(keyed_draw(p.seed, kDomSampler, cur, key_b, sub + 8 * k), dcur.degree, inv);
         if (p.tri)
         {
             // triangle blocks: the filter word of proposal x is the aux word of the slot cur -> x, tested with hash(prev)

@@ -476,62 +476,90 @@ __global__ void __launch_bounds__(256) tri_heavy_kernel(const RowDesc* __restric
     }
 }
 
-// Insert batch, after the merge: one 8-lane group per batch edge (a, b) that is new to the row of a.  With I = N(a) n N(b)
-// in the NEW graph: the slot a -> b gets the block of I; b joined N(a), so for every w in I the set of the slots a -> w and
-// w -> a gained b.  (The twin key (b, a) of a symmetric batch does the same with the roles swapped.)  ORs are idempotent,
-// so edges of one batch that close triangles with each other need no ordering.  Hub - hub edges go to the heavy list.
+// Insert batch, after the merge: one 8-lane group per NEW undirected edge {a, b} - the key (a, b) with a <= b; the batch is
+// symmetric, so its twin key is there too and is skipped: the intersection is the same set.  With I = N(a) n N(b) in the
+// NEW graph: the slots a -> b and b -> a get the block of I; b joined N(a) and a joined N(b), so for every w in I the sets
+// of a -> w, w -> a gained b and those of b -> w, w -> b gained a.  ORs are idempotent, so edges of one batch that close
+// triangles with each other need no ordering.  Hub - hub edges go to the heavy list.
+__device__ __forceinline__ void tri_or(u32* __restrict__ pool, uint2 row, u32 at, u32 bits_hi)
+{
+    atomicOr(pool + row.x + 2 * (u64) at + 1, bits_hi);
+}
+
+__device__ __forceinline__ void tri_or_found(u32* __restrict__ pool, uint2 row, u32 x, u32 bits_hi)       // slot row -> x, if there
+{
+    const u32 r = lower_bound_row(pool + row.x, row.y, x, 1);
+    if (r < row.y && pool[row.x + 2 * (u64) r] == x) tri_or(pool, row, r, bits_hi);
+}
+
+// The members of I found by the lanes `sub` of `lanes`: ORs into the four slots each touches; returns the block bits.
+__device__ __forceinline__ u32 tri_insert_pair(const RowDesc* __restrict__ desc, u32* __restrict__ pool, u32 a, uint2 da, u32 b, uint2 db, u32 sub, u32 lanes)
+{
+    const bool a_small = da.y <= db.y;
+    const uint2 small = a_small ? da : db, large = a_small ? db : da;
+    const u32 bits_a = filter_bits(filter_hash(a)) << 16, bits_b = filter_bits(filter_hash(b)) << 16;
+    u32 bits = 0;
+    for (u32 q = sub; q < small.y; q += lanes)
+    {
+        const u32 w = __ldg(pool + small.x + 2 * (u64) q);
+        const u32 r = lower_bound_row(pool + large.x, large.y, w, 1);
+        if (r >= large.y || __ldg(pool + large.x + 2 * (u64) r) != w) continue;
+        bits |= filter_bits(filter_hash(w));
+        tri_or(pool, da, a_small ? q : r, bits_b);                                                   // a -> w gained b
+        if (a != b) tri_or(pool, db, a_small ? r : q, bits_a);                                       // b -> w gained a
+        const uint2 dw = reinterpret_cast<const uint2*>(desc)[w];
+        tri_or_found(pool, dw, a, bits_b);                                                           // w -> a gained b
+        if (a != b) tri_or_found(pool, dw, b, bits_a);                                               // w -> b gained a
+    }
+    return bits;
+}
+
 __global__ void __launch_bounds__(256) tri_insert_kernel(const u64* __restrict__ keys, u64 k, const u32* __restrict__ change,
                                                          const RowDesc* __restrict__ desc, u32* __restrict__ pool,
                                                          uint2* __restrict__ heavy, u32* __restrict__ heavy_count, u32 heavy_capacity)
 {
     const u64 item = ((u64) blockIdx.x * 256 + threadIdx.x) >> 3;
     const u32 sub = threadIdx.x & 7;
-    const bool has = item < k && change[item];
+    bool has = item < k && change[item];
     u32 a = 0, b = 0;
     uint2 da = make_uint2(0, 0), db = make_uint2(0, 0);
     if (has)
     {
         a = (u32) (keys[item] >> 32);
         b = (u32) keys[item];
+        has = a <= b;                                                                                  // the twin key does nothing
+    }
+    if (has)
+    {
         da = reinterpret_cast<const uint2*>(desc)[a];
         db = reinterpret_cast<const uint2*>(desc)[b];
     }
     const bool is_heavy = has && min(da.y, db.y) > kTriHeavy;
-    u32 bits = 0;
-    if (has && !is_heavy)
-    {
-        const bool a_small = da.y <= db.y;
-        const uint2 small = a_small ? da : db, large = a_small ? db : da;
-        const u32 bits_b = filter_bits(filter_hash(b)) << 16;
-        for (u32 q = sub; q < small.y; q += 8)
-        {
-            const u32 w = __ldg(pool + small.x + 2 * (u64) q);
-            const u32 r = lower_bound_row(pool + large.x, large.y, w, 1);
-            if (r >= large.y || __ldg(pool + large.x + 2 * (u64) r) != w) continue;
-            bits |= filter_bits(filter_hash(w));
-            atomicOr(pool + da.x + 2 * (u64) (a_small ? q : r) + 1, bits_b);                     // slot a -> w
-            const uint2 dw = reinterpret_cast<const uint2*>(desc)[w];
-            const u32 ra = lower_bound_row(pool + dw.x, dw.y, a, 1);
-            if (ra < dw.y && pool[dw.x + 2 * (u64) ra] == a) atomicOr(pool + dw.x + 2 * (u64) ra + 1, bits_b);   // slot w -> a
-        }
-    }
+    u32 bits = (has && !is_heavy) ? tri_insert_pair(desc, pool, a, da, b, db, sub, 8) : 0u;
     bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
     bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
     bits |= __shfl_xor_sync(0xffffffffu, bits, 4);
     if (has && sub == 0)
     {
-        const u32 rb = lower_bound_row(pool + da.x, da.y, b, 1);                                    // slot a -> b
         if (is_heavy)
         {
             const u32 at = atomicAdd(heavy_count, 1u);
-            if (at < heavy_capacity) heavy[at] = make_uint2(a, rb);
-            else if (rb < da.y) atomicOr(pool + da.x + 2 * (u64) rb + 1, 0xFFFF0000u);   // list full: the row of a answers "maybe"
+            if (at < heavy_capacity) heavy[at] = make_uint2(a, b);
+            else                                                                                       // list full: both slots answer "maybe"
+            {
+                tri_or_found(pool, da, b, 0xFFFF0000u);
+                tri_or_found(pool, db, a, 0xFFFF0000u);
+            }
         }
-        else if (bits && rb < da.y) atomicOr(pool + da.x + 2 * (u64) rb + 1, bits << 16);
+        else if (bits)
+        {
+            tri_or_found(pool, da, b, bits << 16);                                                     // slot a -> b
+            if (a != b) tri_or_found(pool, db, a, bits << 16);                                         // slot b -> a
+        }
     }
 }
 
-// Heavy inserted edges: block per edge; slot = (a, index of b in the row of a).
+// Heavy inserted edges {a, b}: a block per edge.
 __global__ void __launch_bounds__(256) tri_insert_heavy_kernel(const RowDesc* __restrict__ desc, u32* __restrict__ pool, const uint2* __restrict__ heavy,
                                                                const u32* __restrict__ heavy_count, u32 heavy_capacity)
 {
@@ -539,30 +567,19 @@ __global__ void __launch_bounds__(256) tri_insert_heavy_kernel(const RowDesc* __
     const u32 count = min(*heavy_count, heavy_capacity);
     for (u32 h = blockIdx.x; h < count; h += gridDim.x)
     {
-        const u32 a = heavy[h].x, rb = heavy[h].y;
+        const u32 a = heavy[h].x, b = heavy[h].y;
         const uint2 da = reinterpret_cast<const uint2*>(desc)[a];
-        const u32 b = pool[da.x + 2 * (u64) rb];
         const uint2 db = reinterpret_cast<const uint2*>(desc)[b];
         if (threadIdx.x == 0) s_bits = 0;
         __syncthreads();
-        const bool a_small = da.y <= db.y;
-        const uint2 small = a_small ? da : db, large = a_small ? db : da;
-        const u32 bits_b = filter_bits(filter_hash(b)) << 16;
-        u32 bits = 0;
-        for (u32 q = threadIdx.x; q < small.y; q += 256)
-        {
-            const u32 w = __ldg(pool + small.x + 2 * (u64) q);
-            const u32 r = lower_bound_row(pool + large.x, large.y, w, 1);
-            if (r >= large.y || __ldg(pool + large.x + 2 * (u64) r) != w) continue;
-            bits |= filter_bits(filter_hash(w));
-            atomicOr(pool + da.x + 2 * (u64) (a_small ? q : r) + 1, bits_b);
-            const uint2 dw = reinterpret_cast<const uint2*>(desc)[w];
-            const u32 ra = lower_bound_row(pool + dw.x, dw.y, a, 1);
-            if (ra < dw.y && pool[dw.x + 2 * (u64) ra] == a) atomicOr(pool + dw.x + 2 * (u64) ra + 1, bits_b);
-        }
+        const u32 bits = tri_insert_pair(desc, pool, a, da, b, db, threadIdx.x, 256);
         if (bits) atomicOr(&s_bits, bits);
         __syncthreads();
-        if (threadIdx.x == 0 && s_bits) atomicOr(pool + da.x + 2 * (u64) rb + 1, s_bits << 16);
+        if (threadIdx.x == 0 && s_bits)
+        {
+            tri_or_found(pool, da, b, s_bits << 16);
+            if (a != b) tri_or_found(pool, db, a, s_bits << 16);
+        }
         __syncthreads();
     }
 }

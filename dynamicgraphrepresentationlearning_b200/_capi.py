@@ -128,6 +128,7 @@ SIGNATURES = {
     "wmh_last_index_ms": (C.c_double, [vp]),
     "wmh_last_search_mode": (u32, [vp]),
     "wmh_neighbour_filter": (u32, [vp]),
+    "wmh_filter_check": (i32, [vp, PU64]),
     "wmh_device_walks": (vp, [vp]),
     "wmh_stream": (vp, [vp]),
     "wmh_synchronize": (i32, [vp]),

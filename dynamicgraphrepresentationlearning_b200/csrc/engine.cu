@@ -1376,6 +1376,17 @@ double wmh_last_walk_kernel_ms(const wmh_engine* e) { return e ? e->last_walk_ke
 double wmh_last_index_ms(const wmh_engine* e) { return e ? e->last_index_ms : 0.0; }
 uint32_t wmh_last_search_mode(const wmh_engine* e) { return e ? e->last_search : 0u; }
 uint32_t wmh_neighbour_filter(const wmh_engine* e) { return (e && e->g.tail) ? (e->g.tri ? 2u : 1u) : 0u; }
+int wmh_filter_check(wmh_engine* e, uint64_t* missing)
+{
+    if (!e || !missing) return fail(WMH_ERR_INVALID, "null argument");
+    return guarded([&] {
+        e->bind();
+        auto lc = e->lc();
+        *missing = graph_filter_check(lc, e->g);
+        return (int) WMH_OK;
+    });
+}
+
 const uint32_t* wmh_device_walks(const wmh_engine* e) { return (e && e->have_walks) ? e->walks.ptr : nullptr; }
 void* wmh_stream(const wmh_engine* e) { return e ? (void*) e->stream : nullptr; }
 

@@ -155,6 +155,7 @@ void graph_compact(const LaunchCtx& lc, DeviceGraph& g, u64 extra_capacity, int 
 // only empty the sampler caches.
 void graph_enable_tails(const LaunchCtx& lc, DeviceGraph& g);
 void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g);
+u64  graph_filter_check(const LaunchCtx& lc, const DeviceGraph& g);      // slots whose membership filter lacks a required bit (must be 0)
 void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g);
 void graph_flatten(const LaunchCtx& lc, const DeviceGraph& g, u64* d_row_ptr /* n+1 */, u32* d_col /* m */);
 // flag |= 1: offsets not monotone / beyond m; 2: a neighbour id >= n; 4: a row not strictly ascending.

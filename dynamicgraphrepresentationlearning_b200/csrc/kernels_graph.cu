@@ -318,6 +318,13 @@ struct TriChunksOf
     __device__ u64 operator()(u64 v) const { return v < count ? (desc[v].degree + kTriChunk - 1) / kTriChunk : 0; }
 };
 
+struct SlotsOfRow
+{
+    const RowDesc* desc;
+    u64 count;
+    __device__ u64 operator()(u64 v) const { return v < count ? (u64) desc[v].degree : 0ull; }
+};
+
 struct DegreeOfRow
 {
     const RowDesc* desc;
@@ -582,6 +589,42 @@ __global__ void __launch_bounds__(256) tri_insert_heavy_kernel(const RowDesc* __
         }
         __syncthreads();
     }
+}
+
+// Self-check of the membership filter (wmh_filter_check): a filter may say "maybe" too often, never "no" wrongly.  Triangle
+// mode: the block of slot v -> c must carry the bits of every w in N(v) n N(c); per-row mode: block filter_block(h(x), deg)
+// of row v must carry the bits of every neighbour x.  One 8-lane group per slot; counts the slots that miss a bit.
+__global__ void __launch_bounds__(256) filter_check_kernel(const RowDesc* __restrict__ desc, const u32* __restrict__ pool, u64 n,
+                                                           const u64* __restrict__ slot_scan, u64 slots, u32 tri, unsigned long long* __restrict__ missing)
+{
+    const u64 slot = ((u64) blockIdx.x * 256 + threadIdx.x) >> 3;
+    const u32 sub = threadIdx.x & 7;
+    if (slot >= slots) return;
+    const u32 v = upper_segment_u64(slot_scan, (u32) n + 1, slot);
+    const uint2 dv = reinterpret_cast<const uint2*>(desc)[v];
+    const u32 i = (u32) (slot - slot_scan[v]);
+    bool bad = false;
+    if (tri)
+    {
+        const u32 c = pool[dv.x + 2 * (u64) i];
+        const u32 block = pool[dv.x + 2 * (u64) i + 1] >> 16;
+        const uint2 dc = reinterpret_cast<const uint2*>(desc)[c];
+        for (u32 q = sub; q < dv.y; q += 8)
+        {
+            const u32 w = pool[dv.x + 2 * (u64) q];
+            const u32 r = lower_bound_row(pool + dc.x, dc.y, w, 1);
+            if (r >= dc.y || pool[dc.x + 2 * (u64) r] != w) continue;
+            const u32 need = filter_bits(filter_hash(w));
+            bad |= (block & need) != need;
+        }
+    }
+    else if (sub == 0)
+    {
+        const u32 h = filter_hash(pool[dv.x + 2 * (u64) i]);
+        const u32 need = filter_bits(h);
+        bad = ((pool[dv.x + 2 * (u64) filter_block(h, dv.y) + 1] >> 16) & need) != need;
+    }
+    if (__ballot_sync(__activemask(), bad) && bad) atomicAdd(missing, 1ull);
 }
 
 // flag |= 1 when some batch key (s, d) has no twin (d, s) in the same (sorted, unique) batch.
@@ -967,6 +1010,34 @@ void graph_aux_rebuild(const LaunchCtx& lc, DeviceGraph& g)
     aux_build_all_kernel<<<div_up(g.n * 32, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.n, g.pool.ptr);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
+}
+
+u64 graph_filter_check(const LaunchCtx& lc, const DeviceGraph& g)
+{
+    if (!g.tail || g.n == 0 || g.m == 0) return 0;
+    Scratch<u64> scan(lc.stream, g.n + 1);
+    Scratch<unsigned long long> missing(lc.stream, 1);
+    {
+        cub::CountingInputIterator<u64> iota(0);
+        cub::TransformInputIterator<u64, SlotsOfRow, cub::CountingInputIterator<u64>> degrees(iota, SlotsOfRow{g.desc.ptr, g.n});
+        size_t bytes = 0;
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, bytes, degrees, scan.ptr, (i64) (g.n + 1), lc.stream));
+        Scratch<u8> temp(lc.stream, bytes);
+        WHARF_CUDA(cub::DeviceScan::ExclusiveSum(temp.ptr, bytes, degrees, scan.ptr, (i64) (g.n + 1), lc.stream));
+        lc.count_lib();
+    }
+    u64 slots = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&slots, scan.ptr + g.n, 8, cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaMemsetAsync(missing.ptr, 0, 8, lc.stream));
+    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
+    if (slots == 0) return 0;
+    filter_check_kernel<<<div_up(slots * 8, 256), 256, 0, lc.stream>>>(g.desc.ptr, g.pool.ptr, g.n, scan.ptr, slots, g.tri, missing.ptr);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+    unsigned long long bad = 0;
+    WHARF_CUDA(cudaMemcpyAsync(&bad, missing.ptr, 8, cudaMemcpyDeviceToHost, lc.stream));
+    WHARF_CUDA(cudaStreamSynchronize(lc.stream));
+    return bad;
 }
 
 void graph_aux_clear_caches(const LaunchCtx& lc, DeviceGraph& g)

@@ -342,6 +342,12 @@ class WharfMH:
         """0: no aux words yet, 1: per-row blocks, 2: triangle blocks (wmh_neighbour_filter)."""
         return int(self._lib.wmh_neighbour_filter(self._h))
 
+    def filter_check(self) -> int:
+        """Edge slots whose membership filter lacks a bit it must carry (wmh_filter_check): 0 on a sound engine."""
+        missing = C.c_uint64()
+        check(self._lib.wmh_filter_check(self._h, C.byref(missing)))
+        return int(missing.value)
+
     def device_walks_ptr(self) -> int:
         return int(self._lib.wmh_device_walks(self._h) or 0)
 

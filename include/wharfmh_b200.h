@@ -287,6 +287,10 @@ WMH_API uint32_t wmh_last_search_mode(const wmh_engine* e);
  * 2 = triangle blocks keyed on the traversed edge (symmetric graph and symmetric batches only; a directed batch drops
  * the engine back to 1).  The filter only prunes exact searches: corpora are identical in every mode. */
 WMH_API uint32_t wmh_neighbour_filter(const wmh_engine* e);
+/* Self-check of that filter (tests): the number of edge slots whose filter block lacks a bit it must carry - triangle mode:
+ * a member of N(v) n N(c) missing from the block of slot v -> c; per-row mode: a neighbour missing from its row's block.
+ * Anything but 0 would make the walk kernel skip an exact search it needs. */
+WMH_API int      wmh_filter_check(wmh_engine* e, uint64_t* missing);
 /* Raw device pointers for zero-copy consumers (position-major walk matrix [L][local_walks]). */
 WMH_API const uint32_t* wmh_device_walks(const wmh_engine* e);
 WMH_API void*    wmh_stream(const wmh_engine* e);                        /* cudaStream_t */

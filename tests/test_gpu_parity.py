@@ -699,6 +699,7 @@ def test_triangle_filter_symmetric_batches_vs_oracle(wharf, wo, init, monkeypatc
             o.update(b.copy(), delete=delete, remove_dups=True)
             (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
             assert e.neighbour_filter() == 2
+            assert e.filter_check() == 0, f"step {step}: a triangle block lost a member"
             assert np.array_equal(e.affected_walks()[0], o.affected()[0])
             assert np.array_equal(e.walks(), o.walks()), f"step {step}"
             corpora.append(e.walks())
@@ -707,12 +708,12 @@ def test_triangle_filter_symmetric_batches_vs_oracle(wharf, wo, init, monkeypatc
         directed = rng.integers(0, n, (40, 2)).astype(np.uint32)      # no reverse edges: the blocks no longer hold
         o.update(directed.copy(), delete=False, remove_dups=True)
         e.insert_edges_batch(directed.copy(), remove_dups=True)
-        assert e.neighbour_filter() == 1
+        assert e.neighbour_filter() == 1 and e.filter_check() == 0
         assert np.array_equal(e.walks(), o.walks())
         b = _sym_pairs(rng.integers(0, n, (50, 2)))
         o.update(b.copy(), delete=False, remove_dups=True)
         e.insert_edges_batch(b.copy(), remove_dups=True)
-        assert e.neighbour_filter() == 1 and np.array_equal(e.walks(), o.walks())
+        assert e.neighbour_filter() == 1 and e.filter_check() == 0 and np.array_equal(e.walks(), o.walks())
     monkeypatch.setenv("WHARF_TRI", "0")
     with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False,
               sampler_init_strategy=ini, seed=5, **kw) as e:
@@ -743,7 +744,7 @@ def test_triangle_filter_hub_rows(wharf, wo, coop, monkeypatch):
         for b, delete in ((_sym_pairs([(0, 2), (1, 2), (5, 6)]), False), (_sym_pairs([(0, 1), (7, 8)]), True), (_sym_pairs([(0, 1)]), False)):
             o.update(b.copy(), delete=delete, remove_dups=True)
             (e.delete_edges_batch if delete else e.insert_edges_batch)(b.copy(), remove_dups=True)
-            assert e.neighbour_filter() == 2 and np.array_equal(e.walks(), o.walks())
+            assert e.neighbour_filter() == 2 and e.filter_check() == 0 and np.array_equal(e.walks(), o.walks())
     directed = pairs[pairs[:, 0] < pairs[:, 1]]                       # one direction only
     doff, dadj = wo.csr_from_sorted_pairs(n, directed)
     o = wo.Oracle(n, doff, dadj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, seed=8, **kw)
@@ -771,12 +772,12 @@ def test_triangle_filter_symmetry_detection(wharf, wo):
         o = wo.Oracle(n, off, adj, model=wo.NODE2VEC, p=0.5, q=2.0, deterministic=False, seed=3, **kw)
         with make(wharf, n, off, adj, random_walk_model=wo.NODE2VEC, paramP=0.5, paramQ=2.0, deterministic_mode=False, seed=3, **kw) as e:
             assert e.generate_initial_random_walks() == o.generate(), name
-            assert e.neighbour_filter() == want, name
+            assert e.neighbour_filter() == want and e.filter_check() == 0, name
             assert np.array_equal(e.walks(), o.walks()), name
             b = _sym_pairs(rng.integers(0, n, (30, 2)))
             o.update(b.copy(), delete=False, remove_dups=True)
             e.insert_edges_batch(b.copy(), remove_dups=True)
-            assert e.neighbour_filter() == want and np.array_equal(e.walks(), o.walks()), name
+            assert e.neighbour_filter() == want and e.filter_check() == 0 and np.array_equal(e.walks(), o.walks()), name
         o.close()
 
 

@@ -600,6 +600,7 @@ __global__ void __launch_bounds__(256) filter_check_kernel(const RowDesc* __rest
     const u64 slot = ((u64) blockIdx.x * 256 + threadIdx.x) >> 3;
     const u32 sub = threadIdx.x & 7;
     if (slot >= slots) return;
+    const u32 group_mask = __activemask();                       // whole 8-lane groups leave together: a lane's partners below are active
     const u32 v = upper_segment_u64(slot_scan, (u32) n + 1, slot);
     const uint2 dv = reinterpret_cast<const uint2*>(desc)[v];
     const u32 i = (u32) (slot - slot_scan[v]);
@@ -624,7 +625,11 @@ __global__ void __launch_bounds__(256) filter_check_kernel(const RowDesc* __rest
         const u32 need = filter_bits(h);
         bad = ((pool[dv.x + 2 * (u64) filter_block(h, dv.y) + 1] >> 16) & need) != need;
     }
-    if (__ballot_sync(__activemask(), bad) && bad) atomicAdd(missing, 1ull);
+    u32 any = bad ? 1u : 0u;
+    any |= __shfl_xor_sync(group_mask, any, 1);
+    any |= __shfl_xor_sync(group_mask, any, 2);
+    any |= __shfl_xor_sync(group_mask, any, 4);
+    if (any && sub == 0) atomicAdd(missing, 1ull);               // one count per slot
 }
 
 // flag |= 1 when some batch key (s, d) has no twin (d, s) in the same (sorted, unique) batch.

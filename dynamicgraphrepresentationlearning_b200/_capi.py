@@ -129,6 +129,7 @@ SIGNATURES = {
     "wmh_last_search_mode": (u32, [vp]),
     "wmh_neighbour_filter": (u32, [vp]),
     "wmh_filter_check": (i32, [vp, PU64]),
+    "wmh_scan_touched_no_alloc": (i32, [vp, vp, u64, vp]),
     "wmh_device_walks": (vp, [vp]),
     "wmh_stream": (vp, [vp]),
     "wmh_synchronize": (i32, [vp]),

@@ -1002,6 +1002,21 @@ int wmh_touched_vertices(wmh_engine* e, uint32_t* out, uint64_t capacity, uint64
     });
 }
 
+int wmh_scan_touched_no_alloc(wmh_engine* e, const uint32_t* d_vertices, uint64_t count, uint32_t* d_min_pos)
+{
+    if (!e || !d_min_pos || (count && !d_vertices)) return fail(WMH_ERR_INVALID, "null argument");
+    if (!e->have_walks) return fail(WMH_ERR_STATE, "walks have not been generated");
+    if (e->g.n > kNoAllocMaxVertices)
+        return fail(WMH_ERR_RANGE, "wmh_scan_touched_no_alloc: the graph has more vertices than its static scratch holds (2^25 = 33554432)");
+    return guarded([&] {
+        e->bind();
+        auto lc = e->lc();
+        walks_scan_touched_no_alloc(lc, e->cfg.device, e->walks.ptr, e->w_local, e->walks_L, e->g.n, d_vertices, count, d_min_pos);
+        WHARF_CUDA(cudaStreamSynchronize(e->stream));
+        return (int) WMH_OK;
+    });
+}
+
 int wmh_walk(wmh_engine* e, uint64_t walk_id, uint32_t* vertices, uint32_t* length)
 {
     if (!e || !vertices) return fail(WMH_ERR_INVALID, "null argument");

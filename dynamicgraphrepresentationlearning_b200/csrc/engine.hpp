@@ -203,6 +203,11 @@ void walks_generate_coalesced(const LaunchCtx& lc, const WalkParams& wp, const u
 void walks_generate_range(const LaunchCtx& lc, const WalkParams& wp, u64 first, u64 count, unsigned long long* d_steps);
 // min_pos[w] = first position whose vertex is in the touched bitmap (kNoPos when none).
 void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, const u32* d_bitmap, u32* d_min_pos);
+// The same with the bitmap in static device memory (no allocation of any kind; at most kNoAllocMaxVertices vertices): marks
+// `count` device-resident vertex ids and scans.  Throws std::length_error beyond the maximum.
+constexpr u64 kNoAllocMaxVertices = 1ull << 25;
+void walks_scan_touched_no_alloc(const LaunchCtx& lc, int device, const u32* d_walks, u64 w_local, u32 L, u64 n, const u32* d_vertices, u64 count,
+                                 u32* d_min_pos);
 // Compacts min_pos != kNoPos into (ids, positions); returns the count.
 u64  walks_compact_affected(const LaunchCtx& lc, const u32* d_min_pos, u64 w_local, u32* d_ids, u32* d_positions);
 void walks_transpose_rows(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u32 L, u64 first, u64 count, u32* d_out);

@@ -7,6 +7,8 @@
 // Layout: the corpus is a position-major matrix walks[L][W_local] of u32 vertex ids, so that the
 // one-walker-per-thread kernels store fully coalesced (lane i writes walks[pos][w0 + i]); a walker that
 // stopped (isolated start / sink) leaves kNoVertex in the remaining cells.
+#include <mutex>
+#include <stdexcept>
 #include "engine.hpp"
 #include "rng.cuh"
 
@@ -1052,6 +1054,53 @@ void walks_scan_touched(const LaunchCtx& lc, const u32* d_walks, u64 w_local, u3
 {
     if (w_local == 0) return;
     scan_touched_kernel<<<div_up(w_local, 256), 256, 0, lc.stream>>>(d_walks, w_local, L, d_bitmap, d_min_pos);
+    lc.count();
+    WHARF_CUDA(cudaGetLastError());
+}
+
+// ---- the same scan with its scratch in static device memory (wmh_scan_touched_no_alloc) ----------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the touched-vertex
+// bitmap the scan needs lives in a file-scope device array instead of a stream-ordered allocation.  Every GPU that loads
+// the library holds these 4 MiB until the process exits.  All calls on a device share the array: a call clears the words it
+// needs before marking, so it never sees an earlier call's bits, but two calls that overlap on the GPU race.
+static __device__ __align__(256) u32 g_static_touched_bitmap[kNoAllocMaxVertices / 32];
+
+__global__ void __launch_bounds__(256) mark_touched_static_kernel(const u32* __restrict__ vertices, u64 count, u64 n, u32* __restrict__ bitmap)
+{
+    const u64 i = (u64) blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    const u32 v = vertices[i];
+    if (v < n) atomicOr(bitmap + (v >> 5), 1u << (v & 31));      // ids beyond the graph name no walker's vertex: ignored
+}
+
+void walks_scan_touched_no_alloc(const LaunchCtx& lc, int device, const u32* d_walks, u64 w_local, u32 L, u64 n, const u32* d_vertices, u64 count,
+                                 u32* d_min_pos)
+{
+    if (n > kNoAllocMaxVertices) throw std::length_error("graph has more vertices than the static scratch of the no-alloc scan holds");
+    // In host code the array's name is a host-side stand-in, not a device address: the address the kernels get is looked up
+    // once per device, with that device current (the caller bound it), and kept.
+    static std::mutex lock;
+    static u32* address[64] = {};
+    if (device < 0 || device >= 64) throw std::length_error("device index beyond the no-alloc scan's table");
+    u32* bitmap = nullptr;
+    {
+        std::lock_guard<std::mutex> guard(lock);
+        if (!address[device])
+        {
+            void* p = nullptr;
+            WHARF_CUDA(cudaGetSymbolAddress(&p, g_static_touched_bitmap));
+            address[device] = static_cast<u32*>(p);
+        }
+        bitmap = address[device];
+    }
+    if (w_local == 0) return;
+    WHARF_CUDA(cudaMemsetAsync(bitmap, 0, ((n + 31) / 32) * sizeof(u32), lc.stream));     // the last call's bits
+    if (count)
+    {
+        mark_touched_static_kernel<<<div_up(count, 256), 256, 0, lc.stream>>>(d_vertices, count, n, bitmap);
+        lc.count();
+    }
+    scan_touched_kernel<<<div_up(w_local, 256), 256, 0, lc.stream>>>(d_walks, w_local, L, bitmap, d_min_pos);
     lc.count();
     WHARF_CUDA(cudaGetLastError());
 }

@@ -213,6 +213,10 @@ class WharfMH:
         check(self._lib.wmh_touched_vertices(self._h, _ptr(out), out.shape[0], C.byref(k)))
         return out
 
+    def scan_touched_no_alloc(self, d_vertices: int, count: int, d_min_pos: int) -> None:
+        """wmh_scan_touched_no_alloc: device pointers in and out, no allocation inside (static scratch, <= 2^25 vertices)."""
+        check(self._lib.wmh_scan_touched_no_alloc(self._h, C.c_void_p(d_vertices), count, C.c_void_p(d_min_pos)))
+
     def walk(self, walk_id: int) -> str:                        # graph/wharfmh.h:365
         need = C.c_size_t()
         check(self._lib.wmh_walk_string(self._h, walk_id, None, 0, C.byref(need)))

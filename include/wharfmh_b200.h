@@ -195,6 +195,17 @@ WMH_API int wmh_affected_walks_global_device(wmh_engine* e, uint64_t* d_ids, uin
 /* Distinct source vertices of the last batch (the vertices whose walks were affected), ascending. */
 WMH_API int wmh_touched_vertices(wmh_engine* e, uint32_t* out, uint64_t capacity, uint64_t* count);
 
+/* No counterpart in the reference: added for callers that cannot allocate (code under
+ * CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The corpus scan of the affected-walk search
+ * (types::MapOfChanges) with its scratch - the touched-vertex bitmap - in a static device array instead of an allocation:
+ * d_min_pos[w] (device, wmh_number_of_local_walks entries) receives the first position at which local walk w stands on
+ * one of the `count` vertices in d_vertices (device; ids >= number_of_vertices are ignored), 0xFFFFFFFF when it never does -
+ * for the source vertices of a batch that is exactly what wmh_affected_walks reports.  Calls no cudaMalloc / cudaFree / pool or
+ * library allocation; runs on the engine's stream and is complete when it returns.  Limits: at most 2^25 = 33554432 vertices
+ * (WMH_ERR_RANGE beyond; the 4 MiB array is held by every GPU that loads the library until the process exits); all calls
+ * on a device share the array, so calls that overlap on the GPU (two engines, two threads) race - serialise them. */
+WMH_API int wmh_scan_touched_no_alloc(wmh_engine* e, const uint32_t* d_vertices, uint64_t count, uint32_t* d_min_pos);
+
 /* WharfMH::walk - graph/wharfmh.h:365: vertices of one walk; *length <= walk_length. */
 WMH_API int wmh_walk(wmh_engine* e, uint64_t walk_id, uint32_t* vertices, uint32_t* length);
 /* The string form walk() returns: "v0 v1 ... v79 " (trailing space).  Returns needed size in *needed. */

@@ -42,6 +42,7 @@ struct DevWalkParams
     u32 L;
     u32 shift;                        // neighbour i of a row sits at pool[begin + (i << shift)] (1: interleaved with aux words)
     u32 coop_search;                  // 1: membership searches in rows of >= kCoopMin neighbours are done by the whole warp
+    u32 spec_desc;                    // 1: load the proposal's descriptor before the accept decision, 0: after it (to_dev picks by graph size)
     u32 tri;                          // 1: the filter half of an aux word is the TRIANGLE block of its slot (kernels_graph.cu); 0: per-row blocks
     u32 init_strategy;
     float inv_p, inv_q;
@@ -484,7 +485,9 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
             const uint2 pair = load_pair(p, d, cslot);
             cand = pair.x;
             cand_aux = pair.y;
-            dcand = load_desc(p.desc, cand);
+            // the accept decision needs the proposal's class, not its descriptor, and 70 % of the proposals are rejected: on
+            // graphs whose descriptors do not fit the L2 it is loaded once the next vertex is known (to_dev)
+            if (p.spec_desc) dcand = load_desc(p.desc, cand);
             cls_new = n2v_prefilter(p, prev, dprev, cand, cand_aux);
             if (cls_new == kClassPending && !(p.coop_search && dprev.degree >= kCoopMin))
             {
@@ -556,8 +559,8 @@ __global__ void __launch_bounds__(kWalkBlock, 4) walk_n2v_kernel(DevWalkParams p
                 const uint2 pair = load_pair(p, d, cslot);
                 next = pair.x;
                 cand_aux = pair.y;
-                dcand = load_desc(p.desc, next);
             }
+            if (!acc || !p.spec_desc) dcand = load_desc(p.desc, next);
             __stcs(out, next);
             prev = cur; dprev = d; cur = next; d = dcand; slot = cslot;
             carried = cand_aux;
@@ -971,6 +974,11 @@ DevWalkParams to_dev(const WalkParams& wp)
     {
         const char* coop = std::getenv("WHARF_COOP_SEARCH");
         p.coop_search = coop && std::atoi(coop) != 0;
+        // descriptor of the proposal before the accept decision (hides its latency; wasted for the 70 % that are rejected) while
+        // the descriptor array sits in the L2 anyway, after it beyond that: scale-20 (8 MB) 23.07 vs 23.46 ms, LiveJournal shape
+        // (39 MB) 111.6 vs 112.2 ms, scale-23 (64 MB) 245.1 vs 238.9 ms - profiles/r02k_spec_desc_ab.txt.  WHARF_SPEC_DESC=0|1 forces.
+        const char* spec = std::getenv("WHARF_SPEC_DESC");
+        p.spec_desc = spec ? (std::atoi(spec) != 0) : (wp.n * sizeof(RowDesc) <= (48ull << 20));
     }
     p.inv_p = 1 / wp.p;                                                 // node2vec.h:78
     p.inv_q = 1 / wp.q;                                                 // node2vec.h:86

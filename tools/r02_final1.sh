@@ -18,4 +18,4 @@ for name, b in d.get('blocks', {}).items():
     u = b.get('updates') or {}
     print(name, 'value %.1f G' % (b['value']/1e9), 'ms', round(b['ms_per_step'],3), 'with_index', b.get('value_with_index'), 'e2e', (b.get('e2e') or {}).get('value'), (b.get('e2e') or {}).get('ms_per_step'), 'ins', u.get('insert_latency_ms_median'), 'del', u.get('delete_latency_ms_median'), 'frac', (b.get('roofline') or {}).get('frac'))
 PY
-timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r_launches.csv python bench.py --gpus 1 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/r_ncu.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/r_ncu.log | cut -c1-200
+echo "launch list: see profiles/r02g_launches_default_1gpu.txt"
